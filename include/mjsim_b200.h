@@ -1,0 +1,81 @@
+/* mjsim_b200.h -- C ABI of libmjsim_b200.so, the drop-in boundary.
+ *
+ * The reference has no FFI for this path: its hot path is the Python class
+ *   DMCEnvironmentAdapter            /root/reference/mujoco_sim/environments/dmc2gym.py:78-168
+ * calling dm_control.composer.Environment.step/reset, which calls MuJoCo's C
+ * engine.  Each entry point below names the reference interface it replaces;
+ * INTEGRATION.md shows the ctypes stub a maintainer would add to dmc2gym.py.
+ *
+ * Conventions: plain pointers and sizes; no torch types.  "d_" pointers are
+ * CUDA device pointers, "h_" pointers are host pointers.  All functions return
+ * 0 on success and a negative value on error (mjs_last_error() has the text).
+ * `stream` is a cudaStream_t passed as void* (NULL = default stream); no call
+ * synchronises the host unless it takes host buffers.
+ */
+#ifndef MJSIM_B200_H_
+#define MJSIM_B200_H_
+
+#include "mjs_model.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct MjsSim MjsSim;
+
+/* Precision of the arithmetic inside the step kernels. */
+#define MJS_PRECISION_F64 0 /* all-double (parity runs)                        */
+#define MJS_PRECISION_MIXED 1 /* FP64 state integration, FP32 dynamics/solver  */
+
+/* Replaces: task construction + `Environment(task, ...)` + MJCF compilation
+ * (mujoco_sim/__init__.py:19-23).  The flattened model/task are copied.
+ * env_offset = global id of this shard's env 0 (multi-GPU: rank * num_envs). */
+int mjs_create(const MjsModel* model, const MjsTask* task, int num_envs, int device, unsigned long long seed,
+               unsigned int env_offset, int precision, MjsSim** out);
+void mjs_destroy(MjsSim* sim);
+
+/* Replaces: DMCEnvironmentAdapter.reset (dmc2gym.py:157-163) for the envs whose
+ * d_mask byte is non-zero (NULL = all).  Samples the task's initial-state boxes
+ * with Philox keyed by (seed, global env id, episode id).  d_obs may be NULL. */
+int mjs_reset(MjsSim* sim, const unsigned char* d_mask, float* d_obs, void* stream);
+
+/* Replaces: DMCEnvironmentAdapter.step (dmc2gym.py:133-155) for all envs.
+ * d_actions [N][A] float32 (NULL: synthetic rollout, actions ~ U(action box)
+ * drawn on device), d_obs [N][O], d_reward [N], d_flags [N][4] bytes
+ * (terminated, truncated, is_success, done), d_final_obs [N][O] or NULL: the
+ * observation of the terminal state when autoreset replaces it in d_obs. */
+int mjs_step(MjsSim* sim, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags,
+             float* d_final_obs, int autoreset, void* stream);
+
+/* Same call with HOST buffers: copies actions H2D, steps, copies results D2H and
+ * synchronises.  This is the end-to-end call the reference-side stub uses. */
+int mjs_step_host(MjsSim* sim, const float* h_actions, float* h_obs, float* h_reward, unsigned char* h_flags,
+                  float* h_final_obs, int autoreset);
+int mjs_reset_host(MjsSim* sim, const unsigned char* h_mask, float* h_obs);
+
+/* Replaces: direct writes to physics.data.qpos/qvel/mocap_pos/ctrl through
+ * physics.bind()/named.data (e.g. pointmass.py:100-130, robot.py:185-189).
+ * AoS MjsEnvState records on the host, envs [first, first+count).
+ * mjs_set_state also re-runs the reset-time mj_forward (warm start) when
+ * `forward` is non-zero. */
+int mjs_set_state(MjsSim* sim, const MjsEnvState* h_states, int first, int count, int forward);
+int mjs_get_state(MjsSim* sim, MjsEnvState* h_states, int first, int count);
+
+/* Episode statistics accumulated by the step kernel since the last call
+ * (SURVEY.md 8e): {return sum, length sum, episodes, successes, truncations,
+ * errors, env-steps, 0}.  d_out may be fed to an NCCL all-reduce directly. */
+int mjs_stats_device(MjsSim* sim, double** d_out);
+int mjs_stats(MjsSim* sim, double* h_out8, int reset);
+
+/* Number of kernels this library launched since creation (bench `gpu_launches`). */
+long long mjs_launch_count(const MjsSim* sim);
+int mjs_num_envs(const MjsSim* sim);
+int mjs_obs_dim(const MjsSim* sim);
+int mjs_action_dim(const MjsSim* sim);
+const char* mjs_last_error(void);
+const char* mjs_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MJSIM_B200_H_ */

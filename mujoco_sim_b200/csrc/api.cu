@@ -1,0 +1,332 @@
+// api.cu -- C ABI of libmjsim_b200.so (include/mjsim_b200.h).
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "../../include/mjsim_b200.h"
+#include "mjs_common.cuh"
+#include "pointmass.cuh"
+#include "arm_api.cuh"
+
+static thread_local char g_err[1024] = "";
+void mjs_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+struct MjsSim {
+  MjsModel model;
+  MjsTask task;
+  int N, device, precision;
+  unsigned long long seed;
+  unsigned int env_offset, step_index;
+  long long launches;
+  double* d_stats;
+  // host-call staging (pinned host + device)
+  float *d_act, *d_obs, *d_rew, *d_fobs, *h_pin;
+  unsigned char *d_flags, *d_mask;
+  cudaStream_t hstream;
+  // PointMass
+  double* pm_sd;
+  int* pm_si;
+  PmParams<double> pm_pd;
+  PmParams<float> pm_pf;
+  // articulated tasks
+  ArmSim* arm;
+};
+
+// ------------------------------------------------------------ host-side helpers
+static void h_quat2mat(double* m, const double* q) {
+  double w = q[0], x = q[1], y = q[2], z = q[3];
+  m[0] = w * w + x * x - y * y - z * z; m[1] = 2 * (x * y - w * z); m[2] = 2 * (x * z + w * y);
+  m[3] = 2 * (x * y + w * z); m[4] = w * w - x * x + y * y - z * z; m[5] = 2 * (y * z - w * x);
+  m[6] = 2 * (x * z - w * y); m[7] = 2 * (y * z + w * x); m[8] = w * w - x * x - y * y + z * z;
+}
+static void h_make_frame(double* f) {
+  auto nrm = [](double* a) { double n = std::sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]); a[0] /= n; a[1] /= n; a[2] /= n; };
+  nrm(f);
+  f[3] = f[4] = f[5] = 0;
+  if (f[1] < 0.5 && f[1] > -0.5) f[4] = 1; else f[5] = 1;
+  double t = f[0] * f[3] + f[1] * f[4] + f[2] * f[5];
+  for (int i = 0; i < 3; i++) f[3 + i] -= t * f[i];
+  nrm(f + 3);
+  f[6] = f[1] * f[5] - f[2] * f[4]; f[7] = f[2] * f[3] - f[0] * f[5]; f[8] = f[0] * f[4] - f[1] * f[3];
+}
+
+// Specialise the flat model into the PointMass kernel's constant block.  The
+// kernel assumes the scene shape of point_reach.py:75-98: one body with two
+// slide joints along world x/y carrying one sphere, static planes, one weld to
+// a mocap body.  Anything else is rejected loudly.
+template <typename real>
+static int build_pm_params(const MjsModel& m, const MjsTask& t, PmParams<real>& P) {
+  memset(&P, 0, sizeof(P));
+  if (m.nv != 2 || m.njnt != 2 || m.neq != 1 || m.nmocap != 1) { mjs_set_error("pointmass kernel: unexpected model shape (nv=%d neq=%d)", m.nv, m.neq); return -1; }
+  int b = t.pm_body;
+  for (int j = 0; j < 2; j++) {
+    const double* ax = m.jnt_axis + 3 * j;
+    if (m.jnt_type[j] != MJS_JNT_SLIDE || m.jnt_body[j] != b || std::fabs(ax[j] - 1.0) > 0 || m.body_parent[b] != 0) { mjs_set_error("pointmass kernel: joints must be world-aligned x/y slides"); return -1; }
+  }
+  const double* bq = m.body_quat + 4 * b;
+  if (bq[0] != 1.0) { mjs_set_error("pointmass kernel: body must be unrotated"); return -1; }
+  double mass = m.body_mass[b];
+  P.m00 = (real)(mass + m.dof_armature[0]); P.m11 = (real)(mass + m.dof_armature[1]); P.m01 = 0;
+  P.timestep = (real)m.timestep;
+  P.n_sub = t.n_sub; P.reward_type = t.reward_type;
+  P.scale = (real)(1.0 / (m.meaninertia * 2));
+  P.max_iter = m.solver_iterations;
+  // all-double runs iterate to the oracle's tolerance; FP32 stops at what FP32 can resolve
+  P.tol = sizeof(real) == 8 ? (real)(m.tolerance * 1e-4) : (real)1e-7;
+  P.body_x = (real)m.body_pos[3 * b]; P.body_y = (real)m.body_pos[3 * b + 1];
+  double bz = m.body_pos[3 * b + 2];
+  P.weld_relx = (real)m.eq_data[3]; P.weld_rely = (real)m.eq_data[4];
+  P.weld_diag = (real)(m.body_invweight0[2 * m.eq_body1[0]] + m.body_invweight0[2 * m.eq_body2[0]]);
+  for (int i = 0; i < 2; i++) P.weld_solref[i] = (real)m.eq_solref[i];
+  for (int i = 0; i < 5; i++) P.weld_solimp[i] = (real)m.eq_solimp[i];
+  P.impratio = (real)m.impratio;
+  int sphere = -1;
+  for (int g = 0; g < m.ngeom; g++) if (m.geom_body[g] == b && m.geom_type[g] == MJS_GEOM_SPHERE) sphere = g;
+  if (sphere < 0) { mjs_set_error("pointmass kernel: no sphere geom"); return -1; }
+  double r = m.geom_size[3 * sphere];
+  for (int p = 0; p < m.npair; p++) {
+    int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
+    if (g2 != sphere || m.geom_type[g1] != MJS_GEOM_PLANE) { mjs_set_error("pointmass kernel: unsupported collision pair"); return -1; }
+    if (P.nplane >= PM_MAXPLANE) { mjs_set_error("pointmass kernel: too many planes"); return -1; }
+    int k = P.nplane++;
+    double R[9], f[9];
+    h_quat2mat(R, m.geom_quat + 4 * g1);
+    double n[3] = {R[2], R[5], R[8]};
+    const double* p0 = m.geom_pos + 3 * g1;
+    // oracle: dist = n.(c - p0) - r  with c = (bx+qx, by+qy, bz)
+    P.pl_nx[k] = (real)n[0]; P.pl_ny[k] = (real)n[1];
+    P.pl_c0[k] = (real)(n[2] * (bz - p0[2]) - n[0] * p0[0] - n[1] * p0[1] - r);
+    f[0] = n[0]; f[1] = n[1]; f[2] = n[2];
+    h_make_frame(f);
+    int dim = m.geom_condim[g1] > m.geom_condim[g2] ? m.geom_condim[g1] : m.geom_condim[g2];
+    if (dim != 3 || m.geom_priority[g1] != m.geom_priority[g2]) { mjs_set_error("pointmass kernel: condim 3 / equal priority only"); return -1; }
+    double mu = std::fmax(m.geom_friction[3 * g1], m.geom_friction[3 * g2]);
+    mu = std::fmax(mu, MJS_MINMU);
+    // body2 = sphere body: Jp = [ex ey]; contact-frame Jacobian = frame[:, 0:2]
+    for (int e = 0; e < 4; e++) {
+      int axis = 1 + e / 2;
+      double sgn = (e % 2 == 0) ? 1.0 : -1.0;
+      for (int c = 0; c < 2; c++) P.pl_J[k][e][c] = (real)(f[c] + sgn * mu * f[3 * axis + c]);
+    }
+    double tran = m.body_invweight0[2 * b] + m.body_invweight0[0];
+    P.pl_diag[k] = (real)(tran + mu * mu * tran);
+    P.pl_mu[k] = (real)mu;
+    P.pl_margin[k] = (real)(std::fmax(m.geom_margin[g1], m.geom_margin[g2]) - std::fmax(m.geom_gap[g1], m.geom_gap[g2]));
+    double x1 = m.geom_solmix[g1], x2 = m.geom_solmix[g2];
+    double mix = (x1 >= MJS_MINVAL && x2 >= MJS_MINVAL) ? x1 / (x1 + x2) : ((x1 < MJS_MINVAL && x2 < MJS_MINVAL) ? 0.5 : (x1 < MJS_MINVAL ? 0.0 : 1.0));
+    const double *r1 = m.geom_solref + 2 * g1, *r2 = m.geom_solref + 2 * g2;
+    for (int i = 0; i < 2; i++) P.pl_solref[k][i] = (real)((r1[0] > 0 && r2[0] > 0) ? mix * r1[i] + (1 - mix) * r2[i] : std::fmin(r1[i], r2[i]));
+    for (int i = 0; i < 5; i++) P.pl_solimp[k][i] = (real)(mix * m.geom_solimp[5 * g1 + i] + (1 - mix) * m.geom_solimp[5 * g2 + i]);
+  }
+  P.lo = (real)t.arena_range[0]; P.hi = (real)t.arena_range[1];
+  P.goal_threshold = (real)t.goal_threshold; P.time_limit = (real)t.time_limit;
+  for (int i = 0; i < 2; i++) {
+    P.spawn_lo[i] = (real)t.spawn_lo[i]; P.spawn_hi[i] = (real)t.spawn_hi[i];
+    P.target_lo[i] = (real)t.target_lo[i]; P.target_hi[i] = (real)t.target_hi[i];
+    P.action_lo[i] = (real)t.action_lo[i]; P.action_hi[i] = (real)t.action_hi[i];
+  }
+  return 0;
+}
+
+static PmIO pm_io(MjsSim* s, const float* act, float* obs, float* rew, unsigned char* flags, float* fobs, int autoreset) {
+  PmIO io;
+  io.sd = s->pm_sd; io.si = s->pm_si; io.actions = act; io.obs = obs; io.reward = rew; io.flags = flags; io.final_obs = fobs;
+  io.stats = s->d_stats; io.N = s->N; io.autoreset = autoreset; io.seed = s->seed; io.env_offset = s->env_offset; io.step_index = s->step_index;
+  return io;
+}
+
+extern "C" {
+
+const char* mjs_last_error(void) { return g_err; }
+const char* mjs_version(void) { return "mjsim_b200 0.1 (sm_100a)"; }
+int mjs_num_envs(const MjsSim* s) { return s->N; }
+int mjs_obs_dim(const MjsSim* s) { return s->task.obs_dim; }
+int mjs_action_dim(const MjsSim* s) { return s->task.action_dim; }
+long long mjs_launch_count(const MjsSim* s) { return s->launches; }
+
+int mjs_create(const MjsModel* model, const MjsTask* task, int num_envs, int device, unsigned long long seed, unsigned int env_offset,
+               int precision, MjsSim** out) {
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    mjs_set_error("mjs_create: no CUDA device -- this library has no CPU fallback");
+    return -2;
+  }
+  MJS_CUDA_CHECK(cudaSetDevice(device));
+  MjsSim* s = new MjsSim();
+  memset(s, 0, sizeof(*s));
+  s->model = *model; s->task = *task; s->N = num_envs; s->device = device; s->seed = seed; s->env_offset = env_offset; s->precision = precision;
+  int N = num_envs, O = task->obs_dim, A = task->action_dim;
+  MJS_CUDA_CHECK(cudaMalloc(&s->d_stats, 8 * sizeof(double)));
+  MJS_CUDA_CHECK(cudaMemset(s->d_stats, 0, 8 * sizeof(double)));
+  MJS_CUDA_CHECK(cudaMalloc(&s->d_act, sizeof(float) * N * A));
+  MJS_CUDA_CHECK(cudaMalloc(&s->d_obs, sizeof(float) * N * O));
+  MJS_CUDA_CHECK(cudaMalloc(&s->d_fobs, sizeof(float) * N * O));
+  MJS_CUDA_CHECK(cudaMalloc(&s->d_rew, sizeof(float) * N));
+  MJS_CUDA_CHECK(cudaMalloc(&s->d_flags, 4 * N));
+  MJS_CUDA_CHECK(cudaMalloc(&s->d_mask, N));
+  MJS_CUDA_CHECK(cudaStreamCreateWithFlags(&s->hstream, cudaStreamNonBlocking));
+  if (task->kind == MJS_TASK_POINTMASS) {
+    if (build_pm_params<double>(*model, *task, s->pm_pd) || build_pm_params<float>(*model, *task, s->pm_pf)) { delete s; return -1; }
+    MJS_CUDA_CHECK(cudaMalloc(&s->pm_sd, sizeof(double) * PM_NFIELD * N));
+    MJS_CUDA_CHECK(cudaMemset(s->pm_sd, 0, sizeof(double) * PM_NFIELD * N));
+    MJS_CUDA_CHECK(cudaMalloc(&s->pm_si, sizeof(int) * PM_I_NFIELD * N));
+    MJS_CUDA_CHECK(cudaMemset(s->pm_si, 0, sizeof(int) * PM_I_NFIELD * N));
+  } else {
+    s->arm = arm_create(*model, *task, N, seed, env_offset, precision, s->d_stats);
+    if (!s->arm) { delete s; return -1; }
+  }
+  *out = s;
+  return 0;
+}
+
+void mjs_destroy(MjsSim* s) {
+  if (!s) return;
+  cudaSetDevice(s->device);
+  cudaFree(s->d_stats); cudaFree(s->d_act); cudaFree(s->d_obs); cudaFree(s->d_fobs); cudaFree(s->d_rew); cudaFree(s->d_flags); cudaFree(s->d_mask);
+  cudaFree(s->pm_sd); cudaFree(s->pm_si);
+  if (s->h_pin) cudaFreeHost(s->h_pin);
+  if (s->arm) arm_destroy(s->arm);
+  cudaStreamDestroy(s->hstream);
+  delete s;
+}
+
+int mjs_reset(MjsSim* s, const unsigned char* d_mask, float* d_obs, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (s->task.kind == MJS_TASK_POINTMASS) {
+    PmIO io = pm_io(s, nullptr, d_obs, nullptr, nullptr, nullptr, 0);
+    int grid = (s->N + 127) / 128;
+    if (s->precision == MJS_PRECISION_F64) pm_reset_kernel<double><<<grid, 128, 0, st>>>(s->pm_pd, io, d_mask);
+    else pm_reset_kernel<float><<<grid, 128, 0, st>>>(s->pm_pf, io, d_mask);
+    s->launches++;
+  } else {
+    int r = arm_reset(s->arm, d_mask, d_obs, st);
+    if (r < 0) return r;
+    s->launches += r;
+  }
+  MJS_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int mjs_step(MjsSim* s, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags, float* d_final_obs, int autoreset, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (s->task.kind == MJS_TASK_POINTMASS) {
+    PmIO io = pm_io(s, d_actions, d_obs, d_reward, d_flags, d_final_obs, autoreset);
+    int grid = (s->N + 127) / 128;
+    if (s->precision == MJS_PRECISION_F64) pm_step_kernel<double><<<grid, 128, 0, st>>>(s->pm_pd, io);
+    else pm_step_kernel<float><<<grid, 128, 0, st>>>(s->pm_pf, io);
+    s->launches++;
+  } else {
+    int r = arm_step(s->arm, d_actions, d_obs, d_reward, d_flags, d_final_obs, autoreset, s->step_index, st);
+    if (r < 0) return r;
+    s->launches += r;
+  }
+  s->step_index++;
+  MJS_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+static int ensure_pin(MjsSim* s) {
+  if (s->h_pin) return 0;
+  size_t n = (size_t)s->N * (s->task.action_dim + 2 * s->task.obs_dim + 1) * sizeof(float) + 4 * (size_t)s->N + s->N;
+  MJS_CUDA_CHECK(cudaMallocHost(&s->h_pin, n));
+  return 0;
+}
+
+int mjs_step_host(MjsSim* s, const float* h_actions, float* h_obs, float* h_reward, unsigned char* h_flags, float* h_final_obs, int autoreset) {
+  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  int N = s->N, A = s->task.action_dim, O = s->task.obs_dim;
+  cudaStream_t st = s->hstream;
+  if (h_actions) MJS_CUDA_CHECK(cudaMemcpyAsync(s->d_act, h_actions, sizeof(float) * N * A, cudaMemcpyHostToDevice, st));
+  int r = mjs_step(s, h_actions ? s->d_act : nullptr, s->d_obs, s->d_rew, s->d_flags, h_final_obs ? s->d_fobs : nullptr, autoreset, st);
+  if (r) return r;
+  MJS_CUDA_CHECK(cudaMemcpyAsync(h_obs, s->d_obs, sizeof(float) * N * O, cudaMemcpyDeviceToHost, st));
+  MJS_CUDA_CHECK(cudaMemcpyAsync(h_reward, s->d_rew, sizeof(float) * N, cudaMemcpyDeviceToHost, st));
+  MJS_CUDA_CHECK(cudaMemcpyAsync(h_flags, s->d_flags, 4 * N, cudaMemcpyDeviceToHost, st));
+  if (h_final_obs) MJS_CUDA_CHECK(cudaMemcpyAsync(h_final_obs, s->d_fobs, sizeof(float) * N * O, cudaMemcpyDeviceToHost, st));
+  MJS_CUDA_CHECK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int mjs_reset_host(MjsSim* s, const unsigned char* h_mask, float* h_obs) {
+  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  cudaStream_t st = s->hstream;
+  if (h_mask) MJS_CUDA_CHECK(cudaMemcpyAsync(s->d_mask, h_mask, s->N, cudaMemcpyHostToDevice, st));
+  int r = mjs_reset(s, h_mask ? s->d_mask : nullptr, s->d_obs, st);
+  if (r) return r;
+  if (h_obs) MJS_CUDA_CHECK(cudaMemcpyAsync(h_obs, s->d_obs, sizeof(float) * s->N * s->task.obs_dim, cudaMemcpyDeviceToHost, st));
+  MJS_CUDA_CHECK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int mjs_set_state(MjsSim* s, const MjsEnvState* h, int first, int count, int forward) {
+  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  MJS_CUDA_CHECK(cudaDeviceSynchronize());
+  int N = s->N;
+  if (first < 0 || count < 0 || first + count > N) { mjs_set_error("mjs_set_state: range out of bounds"); return -1; }
+  if (s->task.kind == MJS_TASK_POINTMASS) {
+    std::vector<double> sd((size_t)PM_NFIELD * N);
+    std::vector<int> si((size_t)PM_I_NFIELD * N);
+    MJS_CUDA_CHECK(cudaMemcpy(sd.data(), s->pm_sd, sd.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    MJS_CUDA_CHECK(cudaMemcpy(si.data(), s->pm_si, si.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < count; i++) {
+      int e = first + i;
+      const MjsEnvState& x = h[i];
+      sd[PM_QX * N + e] = x.qpos[0]; sd[PM_QY * N + e] = x.qpos[1]; sd[PM_VX * N + e] = x.qvel[0]; sd[PM_VY * N + e] = x.qvel[1];
+      sd[PM_MX * N + e] = x.mocap_pos[0]; sd[PM_MY * N + e] = x.mocap_pos[1]; sd[PM_WX * N + e] = x.qacc_warm[0]; sd[PM_WY * N + e] = x.qacc_warm[1];
+      sd[PM_TIME * N + e] = x.time; sd[PM_TX * N + e] = x.target[0]; sd[PM_TY * N + e] = x.target[1];
+      sd[PM_DIST * N + e] = x.dist; sd[PM_PDIST * N + e] = x.prev_dist; sd[PM_RET * N + e] = x.ep_return;
+      si[PM_I_EPISODE * N + e] = x.episode_id; si[PM_I_STATUS * N + e] = x.status; si[PM_I_STEPS * N + e] = x.episode_step;
+    }
+    MJS_CUDA_CHECK(cudaMemcpy(s->pm_sd, sd.data(), sd.size() * sizeof(double), cudaMemcpyHostToDevice));
+    MJS_CUDA_CHECK(cudaMemcpy(s->pm_si, si.data(), si.size() * sizeof(int), cudaMemcpyHostToDevice));
+    (void)forward;  // callers pass the warm start explicitly for PointMass
+    return 0;
+  }
+  return arm_set_state(s->arm, h, first, count, forward);
+}
+
+int mjs_get_state(MjsSim* s, MjsEnvState* h, int first, int count) {
+  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  MJS_CUDA_CHECK(cudaDeviceSynchronize());
+  int N = s->N;
+  if (first < 0 || count < 0 || first + count > N) { mjs_set_error("mjs_get_state: range out of bounds"); return -1; }
+  if (s->task.kind == MJS_TASK_POINTMASS) {
+    std::vector<double> sd((size_t)PM_NFIELD * N);
+    std::vector<int> si((size_t)PM_I_NFIELD * N);
+    MJS_CUDA_CHECK(cudaMemcpy(sd.data(), s->pm_sd, sd.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    MJS_CUDA_CHECK(cudaMemcpy(si.data(), s->pm_si, si.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < count; i++) {
+      int e = first + i;
+      MjsEnvState& x = h[i];
+      memset(&x, 0, sizeof(x));
+      x.qpos[0] = sd[PM_QX * N + e]; x.qpos[1] = sd[PM_QY * N + e]; x.qvel[0] = sd[PM_VX * N + e]; x.qvel[1] = sd[PM_VY * N + e];
+      x.mocap_pos[0] = sd[PM_MX * N + e]; x.mocap_pos[1] = sd[PM_MY * N + e]; x.qacc_warm[0] = sd[PM_WX * N + e]; x.qacc_warm[1] = sd[PM_WY * N + e];
+      x.time = sd[PM_TIME * N + e]; x.target[0] = sd[PM_TX * N + e]; x.target[1] = sd[PM_TY * N + e];
+      x.target[2] = s->task.target_lo[2];
+      x.dist = sd[PM_DIST * N + e]; x.prev_dist = sd[PM_PDIST * N + e]; x.ep_return = sd[PM_RET * N + e];
+      x.episode_id = si[PM_I_EPISODE * N + e]; x.status = si[PM_I_STATUS * N + e]; x.episode_step = si[PM_I_STEPS * N + e];
+    }
+    return 0;
+  }
+  return arm_get_state(s->arm, h, first, count);
+}
+
+int mjs_stats_device(MjsSim* s, double** d_out) { *d_out = s->d_stats; return 0; }
+
+int mjs_stats(MjsSim* s, double* h_out8, int reset) {
+  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  MJS_CUDA_CHECK(cudaDeviceSynchronize());
+  MJS_CUDA_CHECK(cudaMemcpy(h_out8, s->d_stats, 8 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (reset) MJS_CUDA_CHECK(cudaMemset(s->d_stats, 0, 8 * sizeof(double)));
+  return 0;
+}
+
+}  // extern "C"

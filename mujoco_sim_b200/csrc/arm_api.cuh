@@ -1,0 +1,12 @@
+// arm_api.cuh -- host interface of the articulated (warp-per-env) engine.
+#pragma once
+#include "mjs_common.cuh"
+struct ArmSim;
+ArmSim* arm_create(const MjsModel& m, const MjsTask& t, int N, unsigned long long seed, unsigned int env_offset, int precision, double* d_stats);
+void arm_destroy(ArmSim* a);
+// each returns the number of kernels launched (>=0) or a negative error
+int arm_reset(ArmSim* a, const unsigned char* d_mask, float* d_obs, cudaStream_t st);
+int arm_step(ArmSim* a, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags, float* d_final_obs, int autoreset,
+             unsigned int step_index, cudaStream_t st);
+int arm_set_state(ArmSim* a, const MjsEnvState* h, int first, int count, int forward);
+int arm_get_state(ArmSim* a, MjsEnvState* h, int first, int count);

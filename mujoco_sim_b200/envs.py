@@ -1,0 +1,170 @@
+"""Vectorised, GPU-resident mirror of the reference's DMCEnvironmentAdapter.
+
+Reference interface mirrored (per env): /root/reference/mujoco_sim/environments/dmc2gym.py:78-168
+  reset(seed) -> (obs dict, {})                                    :157-163
+  step(a)     -> (obs dict, reward, terminated, truncated, info)   :133-155
+  info = {"is_success": float (tasks with is_goal_reached), "discount": float}
+Observation keys/orders are the reference's.  Everything is a
+torch CUDA tensor with a leading env dimension; auto-reset follows the
+gymnasium "same-step" convention (final observation in info).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import lib as _lib
+from .model import tasks as _tasks
+from .model.cstruct import MjsEnvState
+
+_BUILDERS = {
+    "point_mass_reach": _tasks.build_pointmass_reach,
+}
+
+
+def register_builder(name, fn):
+    _BUILDERS[name] = fn
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+class BatchedMujocoSimEnv:
+    def __init__(self, task_name: str, num_envs: int, device="cuda:0", seed: int = 0, env_offset: int = 0,
+                 precision: str = "mixed", autoreset: bool = True, **task_kwargs):
+        if not torch.cuda.is_available():
+            raise _lib.MjsimError("BatchedMujocoSimEnv needs a CUDA device (there is no CPU fallback)")
+        self.bundle = _BUILDERS[task_name](**task_kwargs)
+        self.task_name = task_name
+        self.num_envs = int(num_envs)
+        self.device = torch.device(device)
+        self.autoreset = autoreset
+        self._L = _lib.load()
+        self._h = ctypes.c_void_p()
+        prec = {"f64": _lib.PRECISION_F64, "mixed": _lib.PRECISION_MIXED}[precision]
+        dev_index = self.device.index or 0
+        _lib.check(self._L.mjs_create(ctypes.byref(self.bundle.model), ctypes.byref(self.bundle.task), self.num_envs, dev_index,
+                                      int(seed) & (2**64 - 1), int(env_offset), prec, ctypes.byref(self._h)))
+        N, O, A = self.num_envs, self.bundle.task.obs_dim, self.bundle.task.action_dim
+        self.obs_dim, self.action_dim = O, A
+        kw = dict(device=self.device)
+        self._obs = torch.zeros(N, O, dtype=torch.float32, **kw)
+        self._final_obs = torch.zeros(N, O, dtype=torch.float32, **kw)
+        self._reward = torch.zeros(N, dtype=torch.float32, **kw)
+        self._flags = torch.zeros(N, 4, dtype=torch.uint8, **kw)
+        self.obs_keys = list(self.bundle.obs_keys)
+        self.has_success = task_name in ("point_mass_reach", "robot_push_button")
+        self.single_action_low = self.bundle.action_low
+        self.single_action_high = self.bundle.action_high
+
+    # ------------------------------------------------------------------ helpers
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _obs_dict(self, flat: torch.Tensor):
+        out, k = {}, 0
+        for key, dim in self.obs_keys:
+            out[key] = flat[:, k : k + dim]
+            k += dim
+        return out
+
+    def close(self):
+        if self._h:
+            self._L.mjs_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---------------------------------------------------------------------- API
+    def reset(self, seed: Optional[int] = None, env_mask: Optional[torch.Tensor] = None):
+        """dmc2gym.py:157-163 for every env (or the masked ones)."""
+        if seed is not None:
+            raise NotImplementedError("re-seeding after construction: create a new env with seed=")
+        mask = None
+        if env_mask is not None:
+            mask = env_mask.to(device=self.device, dtype=torch.uint8).contiguous()
+        _lib.check(self._L.mjs_reset(self._h, _ptr(mask), _ptr(self._obs), self._stream()))
+        return self._obs_dict(self._obs), {}
+
+    def step(self, actions: Optional[torch.Tensor]):
+        """dmc2gym.py:133-155 for every env.  actions=None -> synthetic random rollout."""
+        a = None
+        if actions is not None:
+            a = actions.to(device=self.device, dtype=torch.float32).contiguous()
+            assert a.shape == (self.num_envs, self.action_dim), a.shape
+        _lib.check(self._L.mjs_step(self._h, _ptr(a), _ptr(self._obs), _ptr(self._reward), _ptr(self._flags), _ptr(self._final_obs),
+                                    int(self.autoreset), self._stream()))
+        f = self._flags
+        info = {"discount": 1.0 - f[:, 0].float()}
+        if self.has_success:
+            info["is_success"] = f[:, 2].float()
+        if self.autoreset:
+            info["final_observation"] = self._obs_dict(self._final_obs)
+            info["_final_observation"] = f[:, 3].bool()
+        return self._obs_dict(self._obs), self._reward, f[:, 0].bool(), f[:, 1].bool(), info
+
+    def step_flat(self, actions):
+        """step() without dict assembly: (obs[N,O], reward[N], flags[N,4] u8)."""
+        a = None
+        if actions is not None:
+            a = actions
+        _lib.check(self._L.mjs_step(self._h, _ptr(a), _ptr(self._obs), _ptr(self._reward), _ptr(self._flags), _ptr(self._final_obs),
+                                    int(self.autoreset), self._stream()))
+        return self._obs, self._reward, self._flags
+
+    def step_host(self, actions: np.ndarray, obs: np.ndarray, reward: np.ndarray, flags: np.ndarray):
+        """End-to-end call with HOST numpy buffers (H2D + step + D2H inside the library)."""
+        _lib.check(self._L.mjs_step_host(self._h, actions.ctypes.data_as(ctypes.c_void_p), obs.ctypes.data_as(ctypes.c_void_p),
+                                         reward.ctypes.data_as(ctypes.c_void_p), flags.ctypes.data_as(ctypes.c_void_p), None, int(self.autoreset)))
+
+    # state injection / extraction for parity tests
+    def set_state(self, states, first: int = 0, forward: bool = True):
+        n = len(states)
+        _lib.check(self._L.mjs_set_state(self._h, states, first, n, int(forward)))
+
+    def get_state(self, first: int = 0, count: Optional[int] = None):
+        count = self.num_envs - first if count is None else count
+        arr = (MjsEnvState * count)()
+        _lib.check(self._L.mjs_get_state(self._h, arr, first, count))
+        return arr
+
+    def stats(self, reset: bool = True):
+        out = (ctypes.c_double * 8)()
+        _lib.check(self._L.mjs_stats(self._h, out, int(reset)))
+        keys = ["return_sum", "length_sum", "episodes", "successes", "truncations", "errors", "env_steps", "_"]
+        return dict(zip(keys, list(out)))
+
+    def stats_tensor(self) -> torch.Tensor:
+        """The device-resident [8] f64 accumulator (input of the NCCL all-reduce)."""
+        p = ctypes.c_void_p()
+        _lib.check(self._L.mjs_stats_device(self._h, ctypes.byref(p)))
+        # wrap without copying
+        import torch.utils.dlpack  # noqa: F401
+        from torch import frombuffer  # noqa: F401
+        buf = (ctypes.c_double * 8).from_address(0) if False else None  # pragma: no cover
+        return _wrap_device_f64(p.value, 8, self.device)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._L.mjs_launch_count(self._h))
+
+
+def _wrap_device_f64(ptr: int, n: int, device) -> torch.Tensor:
+    class _Holder:
+        pass
+
+    h = _Holder()
+    h.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+    return torch.as_tensor(h, device=device)
+
+
+def make(task_name: str, num_envs: int, **kw) -> BatchedMujocoSimEnv:
+    return BatchedMujocoSimEnv(task_name, num_envs, **kw)
