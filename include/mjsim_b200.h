@@ -67,6 +67,10 @@ int mjs_get_state(MjsSim* sim, MjsEnvState* h_states, int first, int count);
 int mjs_stats_device(MjsSim* sim, double** d_out);
 int mjs_stats(MjsSim* sim, double* h_out8, int reset);
 
+/* Test hook: mj_forward for one env of an articulated task, dumping intermediate
+ * stages (layout documented at arm_debug_kernel). */
+int mjs_debug_forward(MjsSim* sim, int env, double* h_out, int n);
+
 /* Number of kernels this library launched since creation (bench `gpu_launches`). */
 long long mjs_launch_count(const MjsSim* sim);
 int mjs_num_envs(const MjsSim* sim);

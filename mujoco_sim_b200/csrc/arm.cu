@@ -1,8 +1,164 @@
-// arm.cu -- placeholder until the articulated engine lands.
+// arm.cu -- host side of the articulated (warp-per-env) engine.
+#include <vector>
+
 #include "arm_api.cuh"
-ArmSim* arm_create(const MjsModel&, const MjsTask&, int, unsigned long long, unsigned int, int, double*) { mjs_set_error("articulated engine not built"); return nullptr; }
-void arm_destroy(ArmSim*) {}
-int arm_reset(ArmSim*, const unsigned char*, float*, cudaStream_t) { return -1; }
-int arm_step(ArmSim*, const float*, float*, float*, unsigned char*, float*, int, unsigned int, cudaStream_t) { return -1; }
-int arm_set_state(ArmSim*, const MjsEnvState*, int, int, int) { return -1; }
-int arm_get_state(ArmSim*, MjsEnvState*, int, int) { return -1; }
+#include "arm_kernel.cuh"
+
+#define ARM_WPB 4  // warps (= envs) per thread block
+
+struct ArmSim {
+  int N, nobj, precision;
+  unsigned long long seed;
+  unsigned int env_offset;
+  double* d_stats;
+  double* sd;
+  int* si;
+  int SD, SI;
+  ArmModel<float> mf;
+  ArmModel<double> md;
+  double* d_debug;
+};
+
+template <int NOBJ>
+static void layout_sizes(int& sd, int& si) { sd = ArmLayout<NOBJ>::SD; si = ArmLayout<NOBJ>::SI; }
+
+template <typename real, int NOBJ>
+static int launch(ArmSim* a, const ArmModel<real>& M, int which, ArmIO io, cudaStream_t st, int first = 0, int count = 0) {
+  size_t smem = sizeof(WarpMem<real, NOBJ>) * ARM_WPB;
+  int n = which == 2 ? count : a->N;
+  int grid = (n + ARM_WPB - 1) / ARM_WPB;
+  if (which == 0) {
+    auto k = arm_step_kernel<real, NOBJ, ARM_WPB>;
+    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid, ARM_WPB * 32, smem, st>>>(M, io);
+  } else if (which == 1) {
+    auto k = arm_reset_kernel<real, NOBJ, ARM_WPB>;
+    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid, ARM_WPB * 32, smem, st>>>(M, io);
+  } else if (which == 3) {
+    auto k = arm_debug_kernel<real, NOBJ, ARM_WPB>;
+    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<1, ARM_WPB * 32, smem, st>>>(M, io, first, a->d_debug);
+  } else {
+    auto k = arm_forward_kernel<real, NOBJ, ARM_WPB>;
+    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid, ARM_WPB * 32, smem, st>>>(M, io, first, count);
+  }
+  MJS_CUDA_CHECK(cudaGetLastError());
+  return 1;
+}
+
+static int dispatch(ArmSim* a, int which, ArmIO io, cudaStream_t st, int first = 0, int count = 0) {
+  bool f64 = a->precision == 0;
+  switch (a->nobj) {
+    case 0: return f64 ? launch<double, 0>(a, a->md, which, io, st, first, count) : launch<float, 0>(a, a->mf, which, io, st, first, count);
+    case 3: return f64 ? launch<double, 3>(a, a->md, which, io, st, first, count) : launch<float, 3>(a, a->mf, which, io, st, first, count);
+    default: mjs_set_error("arm engine: built for 0 or 3 props, got %d", a->nobj); return -1;
+  }
+}
+
+ArmSim* arm_create(const MjsModel& m, const MjsTask& t, int N, unsigned long long seed, unsigned int env_offset, int precision, double* d_stats) {
+  ArmSim* a = new ArmSim();
+  a->N = N; a->seed = seed; a->env_offset = env_offset; a->precision = precision; a->d_stats = d_stats;
+  if (build_arm_model<float>(m, t, 0, a->mf) || build_arm_model<double>(m, t, 1, a->md)) { delete a; return nullptr; }
+  a->nobj = a->mf.nobj;
+  if (a->mf.npair + ARM_NLINK > 32) { mjs_set_error("arm engine: npair + 6 limit lanes exceed one warp"); delete a; return nullptr; }
+  if (a->nobj == 0) layout_sizes<0>(a->SD, a->SI);
+  else if (a->nobj == 3) layout_sizes<3>(a->SD, a->SI);
+  else { mjs_set_error("arm engine: built for 0 or 3 props, got %d", a->nobj); delete a; return nullptr; }
+  if (cudaMalloc(&a->sd, sizeof(double) * (size_t)a->SD * N) != cudaSuccess || cudaMalloc(&a->si, sizeof(int) * (size_t)a->SI * N) != cudaSuccess) {
+    mjs_set_error("arm engine: cudaMalloc failed"); delete a; return nullptr;
+  }
+  cudaMalloc(&a->d_debug, sizeof(double) * 1024);
+  cudaMemset(a->sd, 0, sizeof(double) * (size_t)a->SD * N);
+  cudaMemset(a->si, 0, sizeof(int) * (size_t)a->SI * N);
+  return a;
+}
+
+void arm_destroy(ArmSim* a) {
+  if (!a) return;
+  cudaFree(a->sd); cudaFree(a->si);
+  delete a;
+}
+
+static ArmIO make_io(ArmSim* a) {
+  ArmIO io;
+  memset(&io, 0, sizeof(io));
+  io.sd = a->sd; io.si = a->si; io.stats = a->d_stats; io.N = a->N; io.seed = a->seed; io.env_offset = a->env_offset;
+  return io;
+}
+
+int arm_reset(ArmSim* a, const unsigned char* d_mask, float* d_obs, cudaStream_t st) {
+  ArmIO io = make_io(a);
+  io.mask = d_mask; io.obs = d_obs;
+  return dispatch(a, 1, io, st);
+}
+
+int arm_step(ArmSim* a, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags, float* d_final_obs, int autoreset,
+             unsigned int step_index, cudaStream_t st) {
+  ArmIO io = make_io(a);
+  io.actions = d_actions; io.obs = d_obs; io.reward = d_reward; io.flags = d_flags; io.final_obs = d_final_obs;
+  io.autoreset = autoreset; io.step_index = step_index;
+  return dispatch(a, 0, io, st);
+}
+
+template <int NOBJ>
+static void pack(const MjsEnvState& x, double* s, int* si) {
+  using L = ArmLayout<NOBJ>;
+  for (int k = 0; k < L::NQ; k++) s[L::QPOS + k] = x.qpos[k];
+  for (int k = 0; k < L::NV; k++) { s[L::QVEL + k] = x.qvel[k]; s[L::WARM + k] = x.qacc_warm[k]; }
+  for (int k = 0; k < 6; k++) { s[L::CTRL + k] = x.ctrl[k]; s[L::Q0 + k] = x.traj_q0[k]; s[L::Q1 + k] = x.traj_q1[k]; }
+  s[L::TIME] = x.time; s[L::T0] = x.traj_t0; s[L::RET] = x.ep_return;
+  for (int k = 0; k < 3; k++) { s[L::TARGET + k] = x.target[k]; s[L::OVR + k] = x.ovr_pos[k]; }
+  si[L::I_STEP] = x.episode_step; si[L::I_TRAJ] = x.traj_active; si[L::I_SWA] = x.sw_active; si[L::I_SWP] = x.sw_pressed;
+  si[L::I_SWC] = x.sw_count; si[L::I_STATUS] = x.status; si[L::I_EPISODE] = x.episode_id; si[L::I_LEN] = 0;
+}
+template <int NOBJ>
+static void unpack(MjsEnvState& x, const double* s, const int* si) {
+  using L = ArmLayout<NOBJ>;
+  memset(&x, 0, sizeof(x));
+  for (int k = 0; k < L::NQ; k++) x.qpos[k] = s[L::QPOS + k];
+  for (int k = 0; k < L::NV; k++) { x.qvel[k] = s[L::QVEL + k]; x.qacc_warm[k] = s[L::WARM + k]; }
+  for (int k = 0; k < 6; k++) { x.ctrl[k] = s[L::CTRL + k]; x.traj_q0[k] = s[L::Q0 + k]; x.traj_q1[k] = s[L::Q1 + k]; }
+  x.time = s[L::TIME]; x.traj_t0 = s[L::T0]; x.ep_return = s[L::RET];
+  for (int k = 0; k < 3; k++) { x.target[k] = s[L::TARGET + k]; x.ovr_pos[k] = s[L::OVR + k]; }
+  x.episode_step = si[L::I_STEP]; x.traj_active = si[L::I_TRAJ]; x.sw_active = si[L::I_SWA]; x.sw_pressed = si[L::I_SWP];
+  x.sw_count = si[L::I_SWC]; x.status = si[L::I_STATUS]; x.episode_id = si[L::I_EPISODE];
+}
+
+int arm_set_state(ArmSim* a, const MjsEnvState* h, int first, int count, int forward) {
+  std::vector<double> sd((size_t)a->SD * count);
+  std::vector<int> si((size_t)a->SI * count);
+  for (int i = 0; i < count; i++) {
+    if (a->nobj == 0) pack<0>(h[i], sd.data() + (size_t)i * a->SD, si.data() + (size_t)i * a->SI);
+    else pack<3>(h[i], sd.data() + (size_t)i * a->SD, si.data() + (size_t)i * a->SI);
+  }
+  MJS_CUDA_CHECK(cudaMemcpy(a->sd + (size_t)first * a->SD, sd.data(), sd.size() * sizeof(double), cudaMemcpyHostToDevice));
+  MJS_CUDA_CHECK(cudaMemcpy(a->si + (size_t)first * a->SI, si.data(), si.size() * sizeof(int), cudaMemcpyHostToDevice));
+  if (forward) {
+    ArmIO io = make_io(a);
+    if (dispatch(a, 2, io, 0, first, count) < 0) return -1;
+    MJS_CUDA_CHECK(cudaDeviceSynchronize());
+  }
+  return 0;
+}
+
+int arm_get_state(ArmSim* a, MjsEnvState* h, int first, int count) {
+  std::vector<double> sd((size_t)a->SD * count);
+  std::vector<int> si((size_t)a->SI * count);
+  MJS_CUDA_CHECK(cudaMemcpy(sd.data(), a->sd + (size_t)first * a->SD, sd.size() * sizeof(double), cudaMemcpyDeviceToHost));
+  MJS_CUDA_CHECK(cudaMemcpy(si.data(), a->si + (size_t)first * a->SI, si.size() * sizeof(int), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < count; i++) {
+    if (a->nobj == 0) unpack<0>(h[i], sd.data() + (size_t)i * a->SD, si.data() + (size_t)i * a->SI);
+    else unpack<3>(h[i], sd.data() + (size_t)i * a->SD, si.data() + (size_t)i * a->SI);
+  }
+  return 0;
+}
+
+int arm_debug_forward(ArmSim* a, int env, double* h_out, int n) {
+  ArmIO io = make_io(a);
+  if (dispatch(a, 3, io, 0, env, 1) < 0) return -1;
+  MJS_CUDA_CHECK(cudaDeviceSynchronize());
+  MJS_CUDA_CHECK(cudaMemcpy(h_out, a->d_debug, sizeof(double) * (n < 1024 ? n : 1024), cudaMemcpyDeviceToHost));
+  return 0;
+}

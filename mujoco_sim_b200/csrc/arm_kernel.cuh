@@ -1,0 +1,1570 @@
+// arm_kernel.cuh -- ONE WARP PER ENVIRONMENT control-step engine for the
+// "UR arm + free props + static geoms" scenes (Robot Reach, Planar Push,
+// Button Push).  All n_sub physics substeps, the composer hooks, the analytic
+// UR IK, reward/termination/observation assembly and auto-reset run inside one
+// launch; the env state is loaded from HBM once and stored once.
+//
+// Lane roles change per stage (SURVEY.md 8a-2 stage ids in brackets):
+//   [P1] kinematics    lanes 0..5 = links (local transforms in parallel, chain
+//                      composed through shuffles), lane k = free body k, lane g = geom g
+//   [P2,P6] CRB / RNE  lanes 0..5 = links: prefix/suffix scans over the chain
+//   [P4] collision     lane p = candidate geom pair p; warp-scan compaction
+//   [P5] rows          lane c = contact c (contact-frame Jacobian blocks in smem)
+//   [P9] Newton        lane i = dof i for vectors / Hessian rows / Cholesky rows,
+//                      lane c = contact c for cone forces and the line search
+//   [P11] integrator   lane i = dof i
+// No tensor cores: nv <= 30, the work is latency/issue bound FP32 (FP64 for the
+// state integration), see DESIGN.md.
+#pragma once
+#include "arm_model.cuh"
+
+#define FULLMASK 0xffffffffu
+
+template <typename real, int NOBJ>
+struct WarpMem {
+  static constexpr int NV = ARM_NLINK + 6 * NOBJ;
+  static constexpr int NQ = ARM_NLINK + 7 * NOBJ;
+  static constexpr int HS = NV + 1;
+  static constexpr int CS = ARM_MAXC + 1;
+  double qpos[NQ + 1];
+  double qvel[NV];
+  double ctrl[ARM_NLINK];
+  real xpos[ARM_NSLOT][3];
+  real xmat[ARM_NSLOT][9];
+  real gpos[ARM_MAXGEOM][3];
+  real gmat[ARM_MAXGEOM][9];
+  real S[ARM_NLINK][6];         // arm motion axes about the world origin (ang, lin)
+  real Marm[ARM_NLINK][ARM_NLINK];
+  real H[NV][HS];               // Newton Hessian / Cholesky factor (solver order: props first, arm last)
+  real a[NV], dir[NV], qv[NV], fsm[NV], fcon[NV];
+  real cJ[48][CS];              // contact-frame Jacobian blocks: [(side*4 + k)*6 + j][contact]
+  real cf[4][CS];               // contact-space force of the current iterate
+  real cW[7][CS];               // arrow Hessian weights: W00, W01..W03, W11..W33
+  real craw[10][CS];            // dist, pos[3], normal[3], yhint[3]
+  int cpair[ARM_MAXC];
+  int cblk[2][ARM_MAXC];        // dof block of side 0/1: -1 none, 0 arm, 1+k prop k
+  int ccols[2][ARM_MAXC];       // number of arm columns (link+1) when the side is the arm
+  int bcount[1 + ARM_MAXOBJ];
+  int blist[1 + ARM_MAXOBJ][ARM_MAXCB];  // contact | side<<8
+  int ncon;
+  int status;
+};
+
+// ------------------------------------------------------------------ warp helpers
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
+  return v;
+}
+__device__ __forceinline__ float shfl(float v, int src) { return __shfl_sync(FULLMASK, v, src); }
+__device__ __forceinline__ double shfl(double v, int src) { return __shfl_sync(FULLMASK, v, src); }
+__device__ __forceinline__ int shfl(int v, int src) { return __shfl_sync(FULLMASK, v, src); }
+__device__ __forceinline__ float shfl_up(float v, int d) { return __shfl_up_sync(FULLMASK, v, d); }
+__device__ __forceinline__ double shfl_up(double v, int d) { return __shfl_up_sync(FULLMASK, v, d); }
+__device__ __forceinline__ float shfl_down(float v, int d) { return __shfl_down_sync(FULLMASK, v, d); }
+__device__ __forceinline__ double shfl_down(double v, int d) { return __shfl_down_sync(FULLMASK, v, d); }
+
+template <typename real> __device__ __forceinline__ void sincos_r(real x, real* s, real* c);
+template <> __device__ __forceinline__ void sincos_r<float>(float x, float* s, float* c) { sincosf(x, s, c); }
+template <> __device__ __forceinline__ void sincos_r<double>(double x, double* s, double* c) { sincos(x, s, c); }
+template <typename real> __device__ __forceinline__ real rsqrt_r(real x);
+template <> __device__ __forceinline__ float rsqrt_r<float>(float x) { return 1.0f / sqrtf(x); }
+template <> __device__ __forceinline__ double rsqrt_r<double>(double x) { return 1.0 / sqrt(x); }
+
+template <typename real>
+__device__ __forceinline__ void cross3(real* r, const real* a, const real* b) {
+  real x = a[1] * b[2] - a[2] * b[1], y = a[2] * b[0] - a[0] * b[2], z = a[0] * b[1] - a[1] * b[0];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+template <typename real>
+__device__ __forceinline__ real dot3(const real* a, const real* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+template <typename real>
+__device__ __forceinline__ void quat_mul(real* r, const real* a, const real* b) {
+  real w = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
+  real x = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+  real y = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
+  real z = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+  r[0] = w; r[1] = x; r[2] = y; r[3] = z;
+}
+template <typename real>
+__device__ __forceinline__ void quat_norm(real* q) {
+  real n = rsqrt_r<real>(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  q[0] *= n; q[1] *= n; q[2] *= n; q[3] *= n;
+}
+template <typename real>
+__device__ __forceinline__ void quat_to_mat(real* m, const real* q) {
+  real w = q[0], x = q[1], y = q[2], z = q[3];
+  m[0] = w * w + x * x - y * y - z * z; m[1] = 2 * (x * y - w * z); m[2] = 2 * (x * z + w * y);
+  m[3] = 2 * (x * y + w * z); m[4] = w * w - x * x + y * y - z * z; m[5] = 2 * (y * z - w * x);
+  m[6] = 2 * (x * z - w * y); m[7] = 2 * (y * z + w * x); m[8] = w * w - x * x - y * y + z * z;
+}
+template <typename real>
+__device__ __forceinline__ void mat_vec(real* r, const real* m, const real* v) {
+  real x = m[0] * v[0] + m[1] * v[1] + m[2] * v[2], y = m[3] * v[0] + m[4] * v[1] + m[5] * v[2], z = m[6] * v[0] + m[7] * v[1] + m[8] * v[2];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+template <typename real>
+__device__ __forceinline__ void matT_vec(real* r, const real* m, const real* v) {
+  real x = m[0] * v[0] + m[3] * v[1] + m[6] * v[2], y = m[1] * v[0] + m[4] * v[1] + m[7] * v[2], z = m[2] * v[0] + m[5] * v[1] + m[8] * v[2];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+template <typename real>
+__device__ __forceinline__ void cross_motion(real* r, const real* vel, const real* v) {
+  real a[3], b[3], c[3];
+  cross3(a, vel, v); cross3(b, vel, v + 3); cross3(c, vel + 3, v);
+  r[0] = a[0]; r[1] = a[1]; r[2] = a[2]; r[3] = b[0] + c[0]; r[4] = b[1] + c[1]; r[5] = b[2] + c[2];
+}
+template <typename real>
+__device__ __forceinline__ void cross_force(real* r, const real* vel, const real* f) {
+  real a[3], b[3], c[3];
+  cross3(a, vel, f); cross3(b, vel + 3, f + 3); cross3(c, vel, f + 3);
+  r[0] = a[0] + b[0]; r[1] = a[1] + b[1]; r[2] = a[2] + b[2]; r[3] = c[0]; r[4] = c[1]; r[5] = c[2];
+}
+// spatial inertia about the world origin: I[0]=m, I[1..3]=m*com, I[4..9]= xx yy zz xy xz yz
+template <typename real>
+__device__ __forceinline__ void spi_mul(real* f, const real* I, const real* v) {
+  real c[3], t[3];
+  cross3(c, v, I + 1);
+  f[3] = I[0] * v[3] + c[0]; f[4] = I[0] * v[4] + c[1]; f[5] = I[0] * v[5] + c[2];
+  cross3(t, I + 1, v + 3);
+  f[0] = I[4] * v[0] + I[7] * v[1] + I[8] * v[2] + t[0];
+  f[1] = I[7] * v[0] + I[5] * v[1] + I[9] * v[2] + t[1];
+  f[2] = I[8] * v[0] + I[9] * v[1] + I[6] * v[2] + t[2];
+}
+
+template <typename real, int NOBJ>
+struct ArmEngine {
+  using WM = WarpMem<real, NOBJ>;
+  using AM = ArmModel<real>;
+  static constexpr int NV = WM::NV;
+  static constexpr int NQ = WM::NQ;
+
+  // solver ordering: props first, arm last (no fill-in between props)
+  __device__ static __forceinline__ int sidx(int dof) { return dof >= ARM_NLINK ? dof - ARM_NLINK : dof + 6 * NOBJ; }
+  __device__ static __forceinline__ int dof_of_sidx(int s) { return s < 6 * NOBJ ? s + ARM_NLINK : s - 6 * NOBJ; }
+  __device__ static __forceinline__ int blk_base(int blk) { return blk == 0 ? 0 : ARM_NLINK + 6 * (blk - 1); }
+
+  // ------------------------------------------------------------- [P1] kinematics
+  // Restates mj_kinematics for the chain/free-body structure.  Leaves xpos/xmat of
+  // every slot, S (motion axes), geom poses in shared memory.
+  __device__ static void kinematics(const AM& A, WM& W, int lane) {
+    real lq[4] = {1, 0, 0, 0}, lp[3] = {0, 0, 0};
+    if (lane < ARM_NLINK) {
+      real q = (real)W.qpos[lane], s, c;
+      sincos_r<real>(q * (real)0.5, &s, &c);
+      real qr[4] = {c, A.link_axis[lane][0] * s, A.link_axis[lane][1] * s, A.link_axis[lane][2] * s};
+      real bq[4] = {A.link_quat[lane][0], A.link_quat[lane][1], A.link_quat[lane][2], A.link_quat[lane][3]};
+      quat_mul(lq, bq, qr);
+      lp[0] = A.link_pos[lane][0]; lp[1] = A.link_pos[lane][1]; lp[2] = A.link_pos[lane][2];
+    }
+    real cq[4] = {1, 0, 0, 0}, cp[3] = {0, 0, 0};   // running frame (all lanes redundantly)
+    real mq[4] = {1, 0, 0, 0}, mp[3] = {0, 0, 0};   // this lane's link frame
+#pragma unroll
+    for (int i = 0; i < ARM_NLINK; i++) {
+      real q4[4], p3[3];
+#pragma unroll
+      for (int k = 0; k < 4; k++) q4[k] = shfl(lq[k], i);
+#pragma unroll
+      for (int k = 0; k < 3; k++) p3[k] = shfl(lp[k], i);
+      real Rm[9], v[3], nq[4];
+      quat_to_mat(Rm, cq);
+      mat_vec(v, Rm, p3);
+      cp[0] += v[0]; cp[1] += v[1]; cp[2] += v[2];
+      quat_mul(nq, cq, q4);
+      quat_norm(nq);
+#pragma unroll
+      for (int k = 0; k < 4; k++) cq[k] = nq[k];
+      if (lane == i) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) mq[k] = cq[k];
+#pragma unroll
+        for (int k = 0; k < 3; k++) mp[k] = cp[k];
+      }
+    }
+    if (lane < ARM_NLINK) {
+      real Rm[9], ax[3], al[3] = {A.link_axis[lane][0], A.link_axis[lane][1], A.link_axis[lane][2]}, lin[3];
+      quat_to_mat(Rm, mq);
+      mat_vec(ax, Rm, al);
+      cross3(lin, mp, ax);
+#pragma unroll
+      for (int k = 0; k < 3; k++) { W.xpos[SLOT_LINK0 + lane][k] = mp[k]; W.S[lane][k] = ax[k]; W.S[lane][3 + k] = lin[k]; }
+#pragma unroll
+      for (int k = 0; k < 9; k++) W.xmat[SLOT_LINK0 + lane][k] = Rm[k];
+    }
+    if (lane < NOBJ) {
+      int qa = ARM_NLINK + 7 * lane;
+      real q4[4] = {(real)W.qpos[qa + 3], (real)W.qpos[qa + 4], (real)W.qpos[qa + 5], (real)W.qpos[qa + 6]}, Rm[9];
+      quat_norm(q4);
+      quat_to_mat(Rm, q4);
+#pragma unroll
+      for (int k = 0; k < 3; k++) W.xpos[SLOT_OBJ0 + lane][k] = (real)W.qpos[qa + k];
+#pragma unroll
+      for (int k = 0; k < 9; k++) W.xmat[SLOT_OBJ0 + lane][k] = Rm[k];
+    }
+    __syncwarp();
+    if (lane < A.ngeom) {
+      int sl = A.geom_slot[lane];
+      real gp[3] = {A.geom_pos[lane][0], A.geom_pos[lane][1], A.geom_pos[lane][2]}, v[3];
+      const real* R = W.xmat[sl];
+      mat_vec(v, R, gp);
+#pragma unroll
+      for (int k = 0; k < 3; k++) W.gpos[lane][k] = W.xpos[sl][k] + v[k];
+#pragma unroll
+      for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+          W.gmat[lane][3 * r + c] = R[3 * r] * A.geom_mat[lane][c] + R[3 * r + 1] * A.geom_mat[lane][3 + c] + R[3 * r + 2] * A.geom_mat[lane][6 + c];
+    }
+    __syncwarp();
+  }
+
+  // -------------------------------------------- [P2,P6,P7] CRB, RNE bias, actuation
+  // Leaves Marm (joint-space inertia of the chain) and fsm = qfrc_smooth =
+  // qfrc_passive - qfrc_bias + qfrc_actuator for every dof.  Gravity compensation
+  // (robot.py:81-82) is folded into the RNE gravity term: each body feels
+  // (1 - gravcomp) * m * g.  Returns the actuator "force is clamped" flag (lane j).
+  __device__ static bool dynamics(const AM& A, WM& W, int lane) {
+    real Sj[6] = {0, 0, 0, 0, 0, 0}, qd = 0;
+    if (lane < ARM_NLINK) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) Sj[k] = W.S[lane][k];
+      qd = (real)W.qvel[lane];
+    }
+    // inclusive prefix scans along the chain: spatial velocity, then bias acceleration
+    real v[6], acc[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) v[k] = Sj[k] * qd;
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) { real t = shfl_up(v[k], o); if (lane >= o) v[k] += t; }
+    }
+    {
+      real vprev[6], sd[6];
+#pragma unroll
+      for (int k = 0; k < 6; k++) vprev[k] = v[k] - Sj[k] * qd;
+      cross_motion(sd, vprev, Sj);
+#pragma unroll
+      for (int k = 0; k < 6; k++) acc[k] = sd[k] * qd;
+    }
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) { real t = shfl_up(acc[k], o); if (lane >= o) acc[k] += t; }
+    }
+    // inertial bodies (lanes < nab): spatial inertia about the origin + body force
+    real I[10], f[6];
+#pragma unroll
+    for (int k = 0; k < 10; k++) I[k] = 0;
+#pragma unroll
+    for (int k = 0; k < 6; k++) f[k] = 0;
+    int mylink = lane < A.nab ? A.ab_link[lane] : 0;
+    real vb[6], ab[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) { vb[k] = shfl(v[k], mylink); ab[k] = shfl(acc[k], mylink); }
+    if (lane < A.nab) {
+      const real* R = W.xmat[SLOT_LINK0 + mylink];
+      real cl[3] = {A.ab_com[lane][0], A.ab_com[lane][1], A.ab_com[lane][2]}, h[3];
+      mat_vec(h, R, cl);
+      h[0] += W.xpos[SLOT_LINK0 + mylink][0]; h[1] += W.xpos[SLOT_LINK0 + mylink][1]; h[2] += W.xpos[SLOT_LINK0 + mylink][2];
+      // Ic_world = R * Ilocal * R^T
+      real Il[9] = {A.ab_I[lane][0], A.ab_I[lane][3], A.ab_I[lane][4], A.ab_I[lane][3], A.ab_I[lane][1], A.ab_I[lane][5], A.ab_I[lane][4], A.ab_I[lane][5], A.ab_I[lane][2]};
+      real T[9];
+#pragma unroll
+      for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int c = 0; c < 3; c++) T[3 * r + c] = R[3 * r] * Il[c] + R[3 * r + 1] * Il[3 + c] + R[3 * r + 2] * Il[6 + c];
+      real Ic[6];  // xx yy zz xy xz yz
+      Ic[0] = T[0] * R[0] + T[1] * R[1] + T[2] * R[2];
+      Ic[1] = T[3] * R[3] + T[4] * R[4] + T[5] * R[5];
+      Ic[2] = T[6] * R[6] + T[7] * R[7] + T[8] * R[8];
+      Ic[3] = T[0] * R[3] + T[1] * R[4] + T[2] * R[5];
+      Ic[4] = T[0] * R[6] + T[1] * R[7] + T[2] * R[8];
+      Ic[5] = T[3] * R[6] + T[4] * R[7] + T[5] * R[8];
+      real mass = A.ab_mass[lane], hh = dot3(h, h);
+      I[0] = mass; I[1] = mass * h[0]; I[2] = mass * h[1]; I[3] = mass * h[2];
+      I[4] = Ic[0] + mass * (hh - h[0] * h[0]); I[5] = Ic[1] + mass * (hh - h[1] * h[1]); I[6] = Ic[2] + mass * (hh - h[2] * h[2]);
+      I[7] = Ic[3] - mass * h[0] * h[1]; I[8] = Ic[4] - mass * h[0] * h[2]; I[9] = Ic[5] - mass * h[1] * h[2];
+      real fa[6], iv[6], g[6];
+      spi_mul(fa, I, ab);
+      spi_mul(iv, I, vb);
+      cross_force(g, vb, iv);
+      // net gravity (after compensation) as a spatial force at the com
+      real Fg[3] = {A.ab_gfac[lane] * mass * A.gravity[0], A.ab_gfac[lane] * mass * A.gravity[1], A.ab_gfac[lane] * mass * A.gravity[2]}, tg[3];
+      cross3(tg, h, Fg);
+#pragma unroll
+      for (int k = 0; k < 3; k++) { f[k] = fa[k] + g[k] - tg[k]; f[3 + k] = fa[3 + k] + g[3 + k] - Fg[k]; }
+    }
+    // fold the fixed attachments (lanes 6,7) into their link lane
+#pragma unroll
+    for (int a = ARM_NLINK; a < ARM_MAXAB; a++) {
+      int al = shfl(mylink, a);
+      bool take = (a < A.nab) && (lane == al);
+#pragma unroll
+      for (int k = 0; k < 10; k++) { real t = shfl(I[k], a); if (take) I[k] += t; }
+#pragma unroll
+      for (int k = 0; k < 6; k++) { real t = shfl(f[k], a); if (take) f[k] += t; }
+    }
+    if (lane >= ARM_NLINK) {
+#pragma unroll
+      for (int k = 0; k < 10; k++) I[k] = 0;
+#pragma unroll
+      for (int k = 0; k < 6; k++) f[k] = 0;
+    }
+    // suffix scans: composite inertia and accumulated force of the sub-chain
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+#pragma unroll
+      for (int k = 0; k < 10; k++) { real t = shfl_down(I[k], o); if (lane + o < ARM_NLINK) I[k] += t; }
+#pragma unroll
+      for (int k = 0; k < 6; k++) { real t = shfl_down(f[k], o); if (lane + o < ARM_NLINK) f[k] += t; }
+    }
+    bool clamped = false;
+    if (lane < ARM_NLINK) {
+      real tau = 0;
+#pragma unroll
+      for (int k = 0; k < 6; k++) tau += Sj[k] * f[k];
+      real y[6];
+      spi_mul(y, I, Sj);
+#pragma unroll
+      for (int j = 0; j < ARM_NLINK; j++) {
+        real d = 0;
+#pragma unroll
+        for (int k = 0; k < 6; k++) d += W.S[j][k] * y[k];
+        if (j <= lane) {
+          if (j == lane) d += A.armature[lane];
+          W.Marm[lane][j] = d;
+          W.Marm[j][lane] = d;
+        }
+      }
+      // [P7] position actuator in double: kp*(ctrl - q) - kv*qdot, clamped to forcerange
+      double ctrl = W.ctrl[lane];
+      if (A.ctrllimited[lane]) ctrl = fmin(fmax(ctrl, A.ctrl_lo[lane]), A.ctrl_hi[lane]);
+      double frc = A.kp[lane] * (ctrl - W.qpos[lane]) - A.kv[lane] * W.qvel[lane];
+      if (A.forcelimited[lane]) {
+        if (frc <= A.frc_lo[lane]) { frc = A.frc_lo[lane]; clamped = true; }
+        if (frc >= A.frc_hi[lane]) { frc = A.frc_hi[lane]; clamped = true; }
+      }
+      W.fsm[lane] = (real)frc - tau;
+    } else if (lane < NV) {
+      int k = (lane - ARM_NLINK) / 6, d = (lane - ARM_NLINK) % 6;
+      if (d < 3) W.fsm[lane] = A.obj_mass[k] * A.gravity[d];
+      else {
+        int b = ARM_NLINK + 6 * k + 3;
+        real w[3] = {(real)W.qvel[b], (real)W.qvel[b + 1], (real)W.qvel[b + 2]};
+        real Iw[3] = {A.obj_I[k][0] * w[0], A.obj_I[k][1] * w[1], A.obj_I[k][2] * w[2]}, c[3];
+        cross3(c, w, Iw);
+        W.fsm[lane] = -c[d - 3];
+      }
+    }
+    if (lane < NV) W.qv[lane] = (real)W.qvel[lane];
+    __syncwarp();
+    return clamped;
+  }
+
+  // ------------------------------------------------------------- [P4] collision
+  // One lane per candidate pair: bounding-sphere broadphase, analytic narrowphase
+  // (same routines as oracle/mjs_oracle.cpp), warp-scan compaction into W.craw.
+  // Joint-limit rows ride along as pseudo-contacts (cpair = -1 - joint).
+  __device__ static void collide(const AM& A, WM& W, int lane) {
+    int n = 0;
+    real cd[4], cp[4][3], nrm[3] = {0, 0, 1}, yh[3] = {0, 0, 0};
+    int code = lane;  // pair index; limits use -1 - j
+    if (lane < A.npair) {
+      int g1 = A.pair_g1[lane], g2 = A.pair_g2[lane];
+      int t1 = A.geom_type[g1], t2 = A.geom_type[g2];
+      real margin = A.pair_margin[lane];
+      const real *p1 = W.gpos[g1], *p2 = W.gpos[g2], *m1 = W.gmat[g1], *m2 = W.gmat[g2];
+      real s2[3] = {A.geom_size[g2][0], A.geom_size[g2][1], A.geom_size[g2][2]};
+      real dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+      bool pass;
+      if (t1 == MJS_GEOM_PLANE) {
+        nrm[0] = m1[2]; nrm[1] = m1[5]; nrm[2] = m1[8];
+        pass = dot3(dif, nrm) - A.geom_rbound[g2] <= margin;
+      } else {
+        pass = sqrt(dot3(dif, dif)) <= A.geom_rbound[g1] + A.geom_rbound[g2] + margin;
+      }
+      if (pass) {
+        if (t1 == MJS_GEOM_PLANE && t2 == MJS_GEOM_SPHERE) {
+          real dist = dot3(dif, nrm) - s2[0];
+          if (dist <= margin) { cd[0] = dist; for (int k = 0; k < 3; k++) cp[0][k] = p2[k] - nrm[k] * (s2[0] + dist * (real)0.5); n = 1; }
+        } else if (t1 == MJS_GEOM_PLANE && t2 == MJS_GEOM_CAPSULE) {
+          real ax[3] = {m2[2], m2[5], m2[8]};
+          yh[0] = ax[0]; yh[1] = ax[1]; yh[2] = ax[2];
+#pragma unroll
+          for (int e = 0; e < 2; e++) {
+            real sg = e == 0 ? s2[1] : -s2[1];
+            real end[3] = {p2[0] + ax[0] * sg, p2[1] + ax[1] * sg, p2[2] + ax[2] * sg};
+            real d3[3] = {end[0] - p1[0], end[1] - p1[1], end[2] - p1[2]};
+            real dist = dot3(d3, nrm) - s2[0];
+            if (dist <= margin) { cd[n] = dist; for (int k = 0; k < 3; k++) cp[n][k] = end[k] - nrm[k] * (s2[0] + dist * (real)0.5); n++; }
+          }
+        } else if (t1 == MJS_GEOM_PLANE && t2 == MJS_GEOM_CYLINDER) {
+          real ax[3] = {m2[2], m2[5], m2[8]};
+          real prjaxis = dot3(nrm, ax);
+          if (prjaxis > 0) { ax[0] = -ax[0]; ax[1] = -ax[1]; ax[2] = -ax[2]; prjaxis = -prjaxis; }
+          real dist0 = dot3(dif, nrm);
+          real vec[3] = {ax[0] * prjaxis - nrm[0], ax[1] * prjaxis - nrm[1], ax[2] * prjaxis - nrm[2]};
+          real len_sqr = dot3(vec, vec);
+          if (len_sqr >= (real)(MJS_MINVAL * MJS_MINVAL)) {
+            real s = s2[0] / sqrt(len_sqr);
+            vec[0] *= s; vec[1] *= s; vec[2] *= s;
+          } else {
+            vec[0] = m2[0] * s2[0]; vec[1] = m2[3] * s2[0]; vec[2] = m2[6] * s2[0];
+          }
+          real prjvec = dot3(vec, nrm);
+          ax[0] *= s2[1]; ax[1] *= s2[1]; ax[2] *= s2[1];
+          prjaxis *= s2[1];
+          if (dist0 + prjaxis + prjvec <= margin) {
+            real d = dist0 + prjaxis + prjvec;
+            cd[0] = d;
+            for (int k = 0; k < 3; k++) cp[0][k] = p2[k] + vec[k] + ax[k] - nrm[k] * d * (real)0.5;
+            n = 1;
+            if (dist0 - prjaxis + prjvec <= margin) {
+              d = dist0 - prjaxis + prjvec;
+              cd[n] = d;
+              for (int k = 0; k < 3; k++) cp[n][k] = p2[k] + vec[k] - ax[k] - nrm[k] * d * (real)0.5;
+              n++;
+            }
+            real prjvec1 = -prjvec * (real)0.5;
+            if (dist0 + prjaxis + prjvec1 <= margin && n <= 2) {
+              real v1[3];
+              cross3(v1, vec, ax);
+              real l = sqrt(dot3(v1, v1));
+              if (l < (real)MJS_MINVAL) { v1[0] = 1; v1[1] = 0; v1[2] = 0; } else { v1[0] /= l; v1[1] /= l; v1[2] /= l; }
+              real s = s2[0] * (real)0.8660254037844386;  // sqrt(3)/2
+              d = dist0 + prjaxis + prjvec1;
+#pragma unroll
+              for (int e = 0; e < 2; e++) {
+                real sg = e == 0 ? s : -s;
+                cd[n] = d;
+                for (int k = 0; k < 3; k++) cp[n][k] = p2[k] + v1[k] * sg + ax[k] - vec[k] * (real)0.5 - nrm[k] * d * (real)0.5;
+                n++;
+              }
+            }
+          }
+        } else if (t1 == MJS_GEOM_PLANE && t2 == MJS_GEOM_BOX) {
+          real dist = dot3(dif, nrm);
+          for (int i = 0; i < 8 && n < 4; i++) {
+            real vloc[3] = {(i & 1) ? s2[0] : -s2[0], (i & 2) ? s2[1] : -s2[1], (i & 4) ? s2[2] : -s2[2]}, corner[3];
+            mat_vec(corner, m2, vloc);
+            real ldist = dot3(nrm, corner);
+            if (dist + ldist > margin || ldist > 0) continue;
+            cd[n] = dist + ldist;
+            for (int k = 0; k < 3; k++) cp[n][k] = corner[k] + p2[k] - nrm[k] * cd[n] * (real)0.5;
+            n++;
+          }
+        } else {
+          // one-contact pairs: reduce to "sphere(q1,r1) vs sphere(q2,r2)" or an explicit (dist, normal)
+          real q1[3] = {p1[0], p1[1], p1[2]}, q2[3] = {p2[0], p2[1], p2[2]}, r1 = 0, r2 = 0;
+          real s1[3] = {A.geom_size[g1][0], A.geom_size[g1][1], A.geom_size[g1][2]};
+          int mode = 1;  // 1: spheres, 2: explicit result in (cd[0], nrm, cp[0]), 0: nothing
+          if (t1 == MJS_GEOM_SPHERE && t2 == MJS_GEOM_SPHERE) { r1 = s1[0]; r2 = s2[0]; }
+          else if (t1 == MJS_GEOM_SPHERE && t2 == MJS_GEOM_CAPSULE) {
+            real ax[3] = {m2[2], m2[5], m2[8]}, vv[3] = {-dif[0], -dif[1], -dif[2]};
+            real x = fmin(fmax(dot3(ax, vv), -s2[1]), s2[1]);
+            for (int k = 0; k < 3; k++) q2[k] = p2[k] + ax[k] * x;
+            r1 = s1[0]; r2 = s2[0];
+          } else if (t1 == MJS_GEOM_CYLINDER && t2 == MJS_GEOM_CYLINDER) {
+            real a1[3] = {m1[2], m1[5], m1[8]}, a2[3] = {m2[2], m2[5], m2[8]};
+            real tc = dot3(a1, dif), ta = fabs(dot3(a1, a2) * s2[1]);
+            real lo = fmax(-s1[1], tc - ta), hi = fmin(s1[1], tc + ta);
+            if (lo > hi) {
+              real radial[3] = {dif[0] - a1[0] * tc, dif[1] - a1[1] * tc, dif[2] - a1[2] * tc};
+              if (lo - hi <= margin && sqrt(dot3(radial, radial)) < s1[0] + s2[0]) atomicOr(&W.status, MJS_STATUS_UNSUPPORTED_PAIR);
+              mode = 0;
+            } else {
+              real sm = (real)0.5 * (lo + hi);
+              for (int k = 0; k < 3; k++) q1[k] = p1[k] + a1[k] * sm;
+              real w3[3] = {q1[0] - p2[0], q1[1] - p2[1], q1[2] - p2[2]};
+              real u = fmin(fmax(dot3(a2, w3), -s2[1]), s2[1]);
+              for (int k = 0; k < 3; k++) q2[k] = p2[k] + a2[k] * u;
+              r1 = s1[0]; r2 = s2[0];
+            }
+          } else if (t1 == MJS_GEOM_SPHERE && t2 == MJS_GEOM_CYLINDER) {
+            real ax[3] = {m2[2], m2[5], m2[8]}, vv[3] = {-dif[0], -dif[1], -dif[2]};
+            real x = dot3(vv, ax);
+            real perp[3] = {vv[0] - ax[0] * x, vv[1] - ax[1] * x, vv[2] - ax[2] * x};
+            real plen = sqrt(dot3(perp, perp));
+            bool inside_h = fabs(x) <= s2[1], inside_r = plen <= s2[0];
+            real sgn = x >= 0 ? (real)1 : (real)-1;
+            r1 = s1[0];
+            if (inside_h && !inside_r) {
+              for (int k = 0; k < 3; k++) q2[k] = p2[k] + ax[k] * x;
+              r2 = s2[0];
+            } else if (inside_r) {
+              real dist = fabs(x) - s2[1] - r1;
+              mode = 0;
+              if (dist <= margin) {
+                mode = 2; cd[0] = dist;
+                for (int k = 0; k < 3; k++) { nrm[k] = -sgn * ax[k]; cp[0][k] = p1[k] + nrm[k] * (r1 + (real)0.5 * dist); }
+              }
+            } else {
+              for (int k = 0; k < 3; k++) q2[k] = p2[k] + ax[k] * sgn * s2[1] + perp[k] * (s2[0] / plen);
+              r2 = 0;
+            }
+          } else if (t1 == MJS_GEOM_SPHERE && t2 == MJS_GEOM_BOX) {
+            real vv[3] = {-dif[0], -dif[1], -dif[2]}, loc[3], cl[3];
+            matT_vec(loc, m2, vv);
+            bool inside = true;
+            for (int k = 0; k < 3; k++) { cl[k] = fmin(fmax(loc[k], -s2[k]), s2[k]); if (cl[k] != loc[k]) inside = false; }
+            r1 = s1[0];
+            if (!inside) {
+              mat_vec(q2, m2, cl);
+              for (int k = 0; k < 3; k++) q2[k] += p2[k];
+              r2 = 0;
+            } else {
+              int best = 0; real bd = (real)1e30;
+              for (int k = 0; k < 3; k++) { real dd = s2[k] - fabs(loc[k]); if (dd < bd) { bd = dd; best = k; } }
+              real nl[3] = {0, 0, 0};
+              nl[best] = loc[best] >= 0 ? (real)-1 : (real)1;
+              mat_vec(nrm, m2, nl);
+              mode = 2; cd[0] = -bd - r1;
+              for (int k = 0; k < 3; k++) cp[0][k] = p1[k] + nrm[k] * (r1 + (real)0.5 * cd[0]);
+            }
+          } else {
+            atomicOr(&W.status, MJS_STATUS_UNSUPPORTED_PAIR);
+            mode = 0;
+          }
+          if (mode == 1) {
+            real d3[3] = {q2[0] - q1[0], q2[1] - q1[1], q2[2] - q1[2]};
+            real len = sqrt(dot3(d3, d3)), dist = len - r1 - r2;
+            if (dist <= margin) {
+              if (len < (real)MJS_MINVAL) { d3[0] = 1; d3[1] = 0; d3[2] = 0; } else { d3[0] /= len; d3[1] /= len; d3[2] /= len; }
+              cd[0] = dist;
+              for (int k = 0; k < 3; k++) { nrm[k] = d3[k]; cp[0][k] = q1[k] + d3[k] * (r1 + (real)0.5 * dist); }
+              n = 1;
+            }
+          } else if (mode == 2) n = 1;
+        }
+        // mj_collision: contacts with dist >= margin - gap produce no rows
+        real incl = A.pair_incl[lane];
+        int m = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+          if (k < n && cd[k] < incl) { cd[m] = cd[k]; cp[m][0] = cp[k][0]; cp[m][1] = cp[k][1]; cp[m][2] = cp[k][2]; m++; }
+        n = m;
+      }
+    } else if (lane >= A.npair && lane < A.npair + ARM_NLINK) {
+      // joint limits (mj_instantiateLimit)
+      int j = lane - A.npair;
+      if (A.jnt_limited[j]) {
+        real q = (real)W.qpos[j];
+        real dlo = q - A.jnt_lo[j], dhi = A.jnt_hi[j] - q;
+        if (dlo < A.jnt_margin[j]) { n = 1; cd[0] = dlo; cp[0][0] = 1; }
+        else if (dhi < A.jnt_margin[j]) { n = 1; cd[0] = dhi; cp[0][0] = -1; }
+        cp[0][1] = 0; cp[0][2] = 0;
+        code = -1 - j;
+      }
+    }
+    // warp exclusive scan of n
+    int incl_sum = n;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(FULLMASK, incl_sum, o); if (lane >= o) incl_sum += t; }
+    int base = incl_sum - n;
+    int total = __shfl_sync(FULLMASK, incl_sum, 31);
+    if (total > ARM_MAXC) { if (lane == 0) atomicOr(&W.status, MJS_STATUS_CONTACT_OVERFLOW); total = ARM_MAXC; }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      if (k < n && base + k < ARM_MAXC) {
+        int c = base + k;
+        W.craw[0][c] = cd[k];
+        W.craw[1][c] = cp[k][0]; W.craw[2][c] = cp[k][1]; W.craw[3][c] = cp[k][2];
+        W.craw[4][c] = nrm[0]; W.craw[5][c] = nrm[1]; W.craw[6][c] = nrm[2];
+        W.craw[7][c] = yh[0]; W.craw[8][c] = yh[1]; W.craw[9][c] = yh[2];
+        W.cpair[c] = code;
+      }
+    }
+    if (lane == 0) W.ncon = total;
+    if (lane <= ARM_MAXOBJ) W.bcount[lane] = 0;
+    __syncwarp();
+  }
+
+  // per-contact registers that live across the Newton iterations
+  struct ConReg {
+    real D, mu[3], r0, rk[3], e0, ek[3], de0, dek[3];
+    int dim;  // 0: lane has no contact
+  };
+
+  // ----------------------------------------------------------- [P5] constraint rows
+  // Lane c builds contact c: frame, contact-frame Jacobian blocks (side 0 = body1
+  // with sign -1, side 1 = body2), impedance -> D, reference acceleration.
+  __device__ static void make_rows(const AM& A, WM& W, int lane, ConReg& C) {
+    C.dim = 0;
+    C.D = 0; C.r0 = 0; C.e0 = 0; C.de0 = 0;
+#pragma unroll
+    for (int k = 0; k < 3; k++) { C.mu[k] = 0; C.rk[k] = 0; C.ek[k] = 0; C.dek[k] = 0; }
+    int ncon = W.ncon;
+    if (lane < ncon) {
+      int c = lane;
+      int code = W.cpair[c];
+      real dist = W.craw[0][c];
+#pragma unroll 4
+      for (int e = 0; e < 48; e++) W.cJ[e][c] = 0;
+      real u[4] = {0, 0, 0, 0};
+      real kk, bb, imp, incl, diag0;
+      if (code < 0) {
+        int j = -1 - code;
+        real sgn = W.craw[1][c];
+        W.cJ[j][c] = sgn;  // side 0, row 0, column j
+        W.cblk[0][c] = 0; W.ccols[0][c] = ARM_NLINK; W.cblk[1][c] = -1; W.ccols[1][c] = 0;
+        u[0] = sgn * W.qv[j];
+        mjs_kb<real>(A.jnt_solref[j], A.jnt_solimp[j], A.timestep, &kk, &bb);
+        incl = A.jnt_margin[j];
+        imp = mjs_impedance<real>(A.jnt_solimp[j], dist, incl);
+        diag0 = A.jnt_diag[j];
+        C.dim = 1;
+      } else {
+        int p = code;
+        real fr[9] = {W.craw[4][c], W.craw[5][c], W.craw[6][c], W.craw[7][c], W.craw[8][c], W.craw[9][c], 0, 0, 0};
+        real pos[3] = {W.craw[1][c], W.craw[2][c], W.craw[3][c]};
+        // mju_makeFrame
+        {
+          real nn = rsqrt_r<real>(dot3(fr, fr));
+          fr[0] *= nn; fr[1] *= nn; fr[2] *= nn;
+          if (dot3(fr + 3, fr + 3) < (real)0.25) {
+            fr[3] = 0; fr[4] = 0; fr[5] = 0;
+            if (fr[1] < (real)0.5 && fr[1] > (real)-0.5) fr[4] = 1; else fr[5] = 1;
+          }
+          real t = dot3(fr, fr + 3);
+          fr[3] -= t * fr[0]; fr[4] -= t * fr[1]; fr[5] -= t * fr[2];
+          nn = rsqrt_r<real>(dot3(fr + 3, fr + 3));
+          fr[3] *= nn; fr[4] *= nn; fr[5] *= nn;
+          cross3(fr + 6, fr, fr + 3);
+        }
+        int dim = A.pair_dim[p];
+        C.dim = dim;
+        int nrow = dim == 1 ? 1 : dim;  // contact-space rows: normal, 2 tangents, (torsion)
+#pragma unroll
+        for (int side = 0; side < 2; side++) {
+          int g = side == 0 ? A.pair_g1[p] : A.pair_g2[p];
+          int slot = A.geom_slot[g];
+          real sg = side == 0 ? (real)-1 : (real)1;
+          int blk = -1, cols = 0;
+          if (slot >= SLOT_LINK0 && slot < SLOT_LINK0 + ARM_NLINK) {
+            blk = 0; cols = slot - SLOT_LINK0 + 1;
+            for (int j = 0; j < cols; j++) {
+              real Sa[3] = {W.S[j][0], W.S[j][1], W.S[j][2]}, jp[3];
+              cross3(jp, Sa, pos);
+              jp[0] += W.S[j][3]; jp[1] += W.S[j][4]; jp[2] += W.S[j][5];
+              for (int k = 0; k < nrow; k++) {
+                real val = k < 3 ? dot3(fr + 3 * k, jp) : dot3(fr, Sa);
+                W.cJ[(side * 4 + k) * 6 + j][c] = sg * val;
+                u[k] += sg * val * W.qv[j];
+              }
+            }
+          } else if (slot >= SLOT_OBJ0 && slot < SLOT_OBJ0 + ARM_MAXOBJ) {
+            int ob = slot - SLOT_OBJ0;
+            blk = 1 + ob; cols = 6;
+            const real* R = W.xmat[slot];
+            real r[3] = {pos[0] - W.xpos[slot][0], pos[1] - W.xpos[slot][1], pos[2] - W.xpos[slot][2]};
+            int b0 = ARM_NLINK + 6 * ob;
+            for (int k = 0; k < nrow; k++) {
+              for (int j = 0; j < 3; j++) {
+                real val = k < 3 ? fr[3 * k + j] : (real)0;
+                W.cJ[(side * 4 + k) * 6 + j][c] = sg * val;
+                u[k] += sg * val * W.qv[b0 + j];
+              }
+              for (int j = 0; j < 3; j++) {
+                real Ra[3] = {R[j], R[3 + j], R[6 + j]}, jp[3];
+                cross3(jp, Ra, r);
+                real val = k < 3 ? dot3(fr + 3 * k, jp) : dot3(fr, Ra);
+                W.cJ[(side * 4 + k) * 6 + 3 + j][c] = sg * val;
+                u[k] += sg * val * W.qv[b0 + 3 + j];
+              }
+            }
+          }
+          W.cblk[side][c] = blk; W.ccols[side][c] = cols;
+        }
+        C.mu[0] = A.pair_mu[p][0]; C.mu[1] = A.pair_mu[p][0]; C.mu[2] = A.pair_mu[p][1];
+        mjs_kb<real>(A.pair_solref[p], A.pair_solimp[p], A.timestep, &kk, &bb);
+        incl = A.pair_incl[p];
+        imp = mjs_impedance<real>(A.pair_solimp[p], dist, incl);
+        diag0 = dim == 1 ? A.pair_tran[p] : A.pair_tran[p] * (1 + C.mu[0] * C.mu[0]);
+      }
+      real R0 = fmax((real)MJS_MINVAL, (1 - imp) * diag0 / imp);
+      if (C.dim == 1) C.D = 1 / R0;
+      else {
+        real mu = C.mu[0] * rsqrt_r<real>(A.impratio);
+        C.D = 1 / (2 * mu * mu * R0);
+      }
+      // aref rows: r0 +- rk ; jar rows: e0 +- ek with e = (J a) - aref
+      C.r0 = -bb * u[0] - kk * imp * (dist - incl);
+#pragma unroll
+      for (int k = 0; k < 3; k++) C.rk[k] = -bb * C.mu[k] * u[1 + k];
+      // register this contact with the dof blocks it touches
+#pragma unroll
+      for (int side = 0; side < 2; side++) {
+        int blk = W.cblk[side][c];
+        if (blk >= 0) {
+          int slotn = atomicAdd(&W.bcount[blk], 1);
+          if (slotn < ARM_MAXCB) W.blist[blk][slotn] = c | (side << 8);
+          else atomicOr(&W.status, MJS_STATUS_CONTACT_OVERFLOW);
+        }
+      }
+    }
+    __syncwarp();
+    if (lane <= ARM_MAXOBJ && W.bcount[lane] > ARM_MAXCB) W.bcount[lane] = ARM_MAXCB;
+    __syncwarp();
+  }
+
+  // -------------------------------------------------------------- [P9] Newton solve
+  // contact lane: forces, arrow weights and cost of the current e = J a - aref
+  __device__ static __forceinline__ real contact_eval(WM& W, int lane, const ConReg& C, bool write) {
+    real cost = 0;
+    if (C.dim > 0) {
+      real f0 = 0, fk[3] = {0, 0, 0}, w00 = 0, w0k[3] = {0, 0, 0}, wkk[3] = {0, 0, 0};
+      if (C.dim == 1) {
+        real jar = C.e0;
+        if (jar < 0) { f0 = -C.D * jar; w00 = C.D; cost = (real)0.5 * C.D * jar * jar; }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+          if (k < C.dim - 1) {
+            real jp = C.e0 + C.ek[k], jm = C.e0 - C.ek[k];
+            real ap = jp < 0 ? (real)1 : (real)0, am = jm < 0 ? (real)1 : (real)0;
+            real fp = -C.D * jp * ap, fm = -C.D * jm * am;
+            f0 += fp + fm;
+            fk[k] = C.mu[k] * (fp - fm);
+            cost += (real)0.5 * C.D * (jp * jp * ap + jm * jm * am);
+            w00 += C.D * (ap + am);
+            w0k[k] = C.D * C.mu[k] * (ap - am);
+            wkk[k] = C.D * C.mu[k] * C.mu[k] * (ap + am);
+          }
+        }
+      }
+      if (write) {
+        W.cf[0][lane] = f0; W.cf[1][lane] = fk[0]; W.cf[2][lane] = fk[1]; W.cf[3][lane] = fk[2];
+        W.cW[0][lane] = w00; W.cW[1][lane] = w0k[0]; W.cW[2][lane] = w0k[1]; W.cW[3][lane] = w0k[2];
+        W.cW[4][lane] = wkk[0]; W.cW[5][lane] = wkk[1]; W.cW[6][lane] = wkk[2];
+      }
+    }
+    return cost;
+  }
+
+  // contact lane: u = Jc * x for a dof vector x in shared memory (contact space: normal, t1, t2, torsion)
+  __device__ static __forceinline__ void contact_apply(const WM& W, int lane, const ConReg& C, const real* x, real* u) {
+    u[0] = u[1] = u[2] = u[3] = 0;
+    if (C.dim > 0) {
+#pragma unroll
+      for (int side = 0; side < 2; side++) {
+        int blk = W.cblk[side][lane];
+        if (blk < 0) continue;
+        int b0 = blk_base(blk), cols = W.ccols[side][lane];
+        for (int j = 0; j < cols; j++) {
+          real xj = x[b0 + j];
+#pragma unroll
+          for (int k = 0; k < 4; k++) u[k] += W.cJ[(side * 4 + k) * 6 + j][lane] * xj;
+        }
+      }
+    }
+  }
+
+  // dof lane: (J^T f)_i over the contacts of this dof's block
+  __device__ static __forceinline__ real jt_force(const WM& W, int myblk, int d) {
+    real s = 0;
+    int n = W.bcount[myblk];
+    for (int r = 0; r < n; r++) {
+      int e = W.blist[myblk][r], c = e & 0xff, side = e >> 8;
+#pragma unroll
+      for (int k = 0; k < 4; k++) s += W.cJ[(side * 4 + k) * 6 + d][c] * W.cf[k][c];
+    }
+    return s;
+  }
+
+  // Primal Newton with a safeguarded-Newton exact line search (cost is piecewise
+  // quadratic).  On exit W.a = qacc, W.fcon = qfrc_constraint.  Returns iterations.
+  __device__ static int solve(const AM& A, WM& W, int lane, ConReg& C, real& a_i) {
+    const int myblk = lane < ARM_NLINK ? 0 : 1 + (lane - ARM_NLINK) / 6;
+    const int d = lane < ARM_NLINK ? lane : (lane - ARM_NLINK) % 6;
+    const bool isdof = lane < NV;
+    const int si = isdof ? sidx(lane) : 0;
+    const int ncon = W.ncon;
+    real mdiag = 0;
+    if (isdof && lane >= ARM_NLINK) { int k = (lane - ARM_NLINK) / 6; mdiag = d < 3 ? A.obj_mass[k] : A.obj_I[k][d - 3]; }
+    if (isdof) W.a[lane] = a_i;
+    __syncwarp();
+    // e = J a - aref
+    {
+      real u[4];
+      contact_apply(W, lane, C, W.a, u);
+      C.e0 = u[0] - C.r0;
+#pragma unroll
+      for (int k = 0; k < 3; k++) C.ek[k] = C.mu[k] * u[1 + k] - C.rk[k];
+    }
+    real prev_cost = 0;
+    int it = 0;
+    const real fsm_i = isdof ? W.fsm[lane] : (real)0;
+    for (; it < A.max_iter; it++) {
+      real ccost = contact_eval(W, lane, C, true);
+      __syncwarp();
+      // gradient and cost
+      real Ma = 0, grad = 0;
+      if (isdof) {
+        if (lane < ARM_NLINK) {
+#pragma unroll
+          for (int j = 0; j < ARM_NLINK; j++) Ma += W.Marm[lane][j] * W.a[j];
+        } else Ma = mdiag * a_i;
+        grad = Ma - fsm_i - jt_force(W, myblk, d);
+      }
+      real cost = warp_sum(ccost + (isdof ? a_i * ((real)0.5 * Ma - fsm_i) : (real)0));
+      real gn = sqrt(warp_sum(grad * grad));
+      if (it > 0 && (prev_cost - cost) * A.scale < A.tol) break;
+      if (gn * A.scale < A.tol) break;
+      prev_cost = cost;
+      // ---- Hessian rows H = M + sum_c Jc^T W_c Jc (solver ordering)
+      if (isdof) {
+        for (int j = 0; j < NV; j++) W.H[si][j] = 0;
+        if (lane < ARM_NLINK) {
+#pragma unroll
+          for (int j = 0; j < ARM_NLINK; j++) W.H[si][sidx(j)] = W.Marm[lane][j];
+        } else W.H[si][si] = mdiag;
+        int n = W.bcount[myblk];
+        for (int r = 0; r < n; r++) {
+          int e = W.blist[myblk][r], c = e & 0xff, side = e >> 8;
+          real jm[4], z[4];
+#pragma unroll
+          for (int k = 0; k < 4; k++) jm[k] = W.cJ[(side * 4 + k) * 6 + d][c];
+          z[0] = W.cW[0][c] * jm[0] + W.cW[1][c] * jm[1] + W.cW[2][c] * jm[2] + W.cW[3][c] * jm[3];
+#pragma unroll
+          for (int k = 0; k < 3; k++) z[1 + k] = W.cW[1 + k][c] * jm[0] + W.cW[4 + k][c] * jm[1 + k];
+#pragma unroll
+          for (int s2 = 0; s2 < 2; s2++) {
+            int blk2 = W.cblk[s2][c];
+            if (blk2 < 0) continue;
+            int b2 = blk_base(blk2), cols2 = W.ccols[s2][c];
+            for (int j = 0; j < cols2; j++) {
+              real t = 0;
+#pragma unroll
+              for (int k = 0; k < 4; k++) t += z[k] * W.cJ[(s2 * 4 + k) * 6 + j][c];
+              W.H[si][sidx(b2 + j)] += t;
+            }
+          }
+        }
+      }
+      __syncwarp();
+      // ---- Cholesky H = L L^T, lane = row, left-looking by column
+      real rdiag = 1;
+      for (int k = 0; k < NV; k++) {
+        real s = 0;
+        if (isdof && si >= k) {
+          s = W.H[si][k];
+          for (int j = 0; j < k; j++) s -= W.H[si][j] * W.H[k][j];
+        }
+        int owner = dof_of_sidx(k);
+        real dk = shfl(s, owner);
+        real rd = rsqrt_r<real>(dk);
+        if (isdof) {
+          if (si == k) { W.H[si][k] = dk * rd; rdiag = rd; }
+          else if (si > k) W.H[si][k] = s * rd;
+        }
+        __syncwarp();
+      }
+      // ---- solve L L^T dir = -grad
+      real b = -grad;
+      for (int k = 0; k < NV; k++) {
+        int owner = dof_of_sidx(k);
+        real yk = shfl(b * rdiag, owner);
+        if (isdof) { if (si == k) b = yk; else if (si > k) b -= W.H[si][k] * yk; }
+      }
+      for (int k = NV - 1; k >= 0; k--) {
+        int owner = dof_of_sidx(k);
+        real xk = shfl(b * rdiag, owner);
+        if (isdof) { if (si == k) b = xk; else if (si < k) b -= W.H[k][si] * xk; }
+      }
+      real dir_i = isdof ? b : (real)0;
+      if (isdof) W.dir[lane] = dir_i;
+      __syncwarp();
+      // ---- exact line search along dir
+      real Md = 0;
+      if (isdof) {
+        if (lane < ARM_NLINK) {
+#pragma unroll
+          for (int j = 0; j < ARM_NLINK; j++) Md += W.Marm[lane][j] * W.dir[j];
+        } else Md = mdiag * dir_i;
+      }
+      real q1 = warp_sum(isdof ? dir_i * (Ma - fsm_i) : (real)0);
+      real q2 = warp_sum(isdof ? dir_i * Md : (real)0);
+      {
+        real u[4];
+        contact_apply(W, lane, C, W.dir, u);
+        C.de0 = u[0];
+#pragma unroll
+        for (int k = 0; k < 3; k++) C.dek[k] = C.mu[k] * u[1 + k];
+      }
+      real alpha = 0, lo = 0, hi = (real)-1, s_lo = 0;
+      real s0abs = 0;
+      const int LSMAX = sizeof(real) == 8 ? 40 : 12;
+      for (int ls = 0; ls < LSMAX; ls++) {
+        // derivative and curvature of the cost at alpha
+        real sl = 0, cu = 0;
+        if (C.dim == 1) {
+          real jar = C.e0 + alpha * C.de0;
+          if (jar < 0 || (jar == 0 && C.de0 < 0)) { sl = C.D * jar * C.de0; cu = C.D * C.de0 * C.de0; }
+        } else if (C.dim > 1) {
+#pragma unroll
+          for (int k = 0; k < 3; k++) {
+            if (k < C.dim - 1) {
+              real jp = C.e0 + C.ek[k] + alpha * (C.de0 + C.dek[k]), dp = C.de0 + C.dek[k];
+              real jm = C.e0 - C.ek[k] + alpha * (C.de0 - C.dek[k]), dm = C.de0 - C.dek[k];
+              if (jp < 0 || (jp == 0 && dp < 0)) { sl += C.D * jp * dp; cu += C.D * dp * dp; }
+              if (jm < 0 || (jm == 0 && dm < 0)) { sl += C.D * jm * dm; cu += C.D * dm * dm; }
+            }
+          }
+        }
+        sl = warp_sum(sl) + q1 + alpha * q2;
+        cu = warp_sum(cu) + q2;
+        if (ls == 0) s0abs = fabs(sl);
+        const real lstol = sizeof(real) == 8 ? (real)1e-14 : (real)1e-6;
+        if (fabs(sl) <= lstol * s0abs || cu <= 0) break;
+        if (sl < 0) { lo = alpha; s_lo = sl; } else hi = alpha;
+        real an = alpha - sl / cu;
+        if (hi >= 0 && !(an > lo && an < hi)) an = (real)0.5 * (lo + hi);
+        if (an == alpha) break;
+        alpha = an;
+      }
+      (void)s_lo;
+      a_i += alpha * dir_i;
+      if (isdof) W.a[lane] = a_i;
+      C.e0 += alpha * C.de0;
+#pragma unroll
+      for (int k = 0; k < 3; k++) C.ek[k] += alpha * C.dek[k];
+      __syncwarp();
+    }
+    // final forces -> qfrc_constraint
+    contact_eval(W, lane, C, true);
+    __syncwarp();
+    if (isdof) W.fcon[lane] = jt_force(W, myblk, d);
+    __syncwarp();
+    return it;
+  }
+
+  // ----------------------------------------------------- [P10] touch sensor (mj_sensorAcc)
+  __device__ static real touch_force(const AM& A, const WM& W, int lane, const ConReg& C) {
+    real f = 0;
+    if (A.touch_slot >= 0 && C.dim > 0 && W.cpair[lane] >= 0 && ((A.touch_pair_mask >> W.cpair[lane]) & 1)) {
+      real fn = W.cf[0][lane];
+      if (fn > 0) {
+        const real* R = W.xmat[A.touch_slot];
+        real sp[3], sm[9], v[3];
+        real tp[3] = {A.touch_pos[0], A.touch_pos[1], A.touch_pos[2]};
+        mat_vec(v, R, tp);
+        for (int k = 0; k < 3; k++) sp[k] = W.xpos[A.touch_slot][k] + v[k];
+        for (int r = 0; r < 3; r++)
+          for (int c = 0; c < 3; c++) sm[3 * r + c] = R[3 * r] * A.touch_mat[c] + R[3 * r + 1] * A.touch_mat[3 + c] + R[3 * r + 2] * A.touch_mat[6 + c];
+        real dif[3] = {W.craw[1][lane] - sp[0], W.craw[2][lane] - sp[1], W.craw[3][lane] - sp[2]}, loc[3];
+        matT_vec(loc, sm, dif);
+        if (loc[0] * loc[0] + loc[1] * loc[1] <= A.touch_size[0] * A.touch_size[0] && fabs(loc[2]) <= A.touch_size[1]) f = fn;
+      }
+    }
+    return warp_sum(f);
+  }
+
+  // ------------------------------------------------- [P11] implicitfast / Euler + advance
+  // (M - h dF/dv) qacc' = qfrc_smooth + qfrc_constraint; dF/dv = -kv of unclamped
+  // actuators (mjd_actuator_vel).  Props have no velocity-dependent forces.
+  __device__ static void integrate(const AM& A, WM& W, int lane, bool clamped, double& time) {
+    const real h = A.timestep;
+    real qacc = 0;
+    if (lane < ARM_NLINK) {
+      real dv = (A.integrator == MJS_INT_IMPLICITFAST && !clamped) ? (real)A.kv[lane] : (real)0;
+      // 6x6 system in the (now free) Hessian scratch, lanes 0..5 = rows
+#pragma unroll
+      for (int j = 0; j < ARM_NLINK; j++) W.H[lane][j] = W.Marm[lane][j] + (j == lane ? h * dv : (real)0);
+    }
+    __syncwarp();
+    real rdiag = 1;
+#pragma unroll
+    for (int k = 0; k < ARM_NLINK; k++) {
+      real s = 0;
+      if (lane < ARM_NLINK && lane >= k) {
+        s = W.H[lane][k];
+        for (int j = 0; j < k; j++) s -= W.H[lane][j] * W.H[k][j];
+      }
+      real dk = shfl(s, k);
+      real rd = rsqrt_r<real>(dk);
+      if (lane < ARM_NLINK) {
+        if (lane == k) { W.H[lane][k] = dk * rd; rdiag = rd; }
+        else if (lane > k) W.H[lane][k] = s * rd;
+      }
+      __syncwarp();
+    }
+    real b = lane < NV ? W.fsm[lane] + W.fcon[lane] : (real)0;
+#pragma unroll
+    for (int k = 0; k < ARM_NLINK; k++) {
+      real yk = shfl(b * rdiag, k);
+      if (lane < ARM_NLINK) { if (lane == k) b = yk; else if (lane > k) b -= W.H[lane][k] * yk; }
+    }
+#pragma unroll
+    for (int k = ARM_NLINK - 1; k >= 0; k--) {
+      real xk = shfl(b * rdiag, k);
+      if (lane < ARM_NLINK) { if (lane == k) b = xk; else if (lane < k) b -= W.H[k][lane] * xk; }
+    }
+    if (lane < ARM_NLINK) qacc = b;
+    else if (lane < NV) {
+      int k = (lane - ARM_NLINK) / 6, d = (lane - ARM_NLINK) % 6;
+      qacc = b / (d < 3 ? A.obj_mass[k] : A.obj_I[k][d - 3]);
+    }
+    // mj_advance in double
+    if (lane < NV) W.qvel[lane] += (double)h * (double)qacc;
+    __syncwarp();
+    if (lane < ARM_NLINK) W.qpos[lane] += (double)h * W.qvel[lane];
+    else if (lane < NV) {
+      int k = (lane - ARM_NLINK) / 6, d = (lane - ARM_NLINK) % 6;
+      int qa = ARM_NLINK + 7 * k, da = ARM_NLINK + 6 * k;
+      if (d < 3) W.qpos[qa + d] += (double)h * W.qvel[da + d];
+      else if (d == 3) {
+        // quaternion exponential map: q <- q * exp(h * omega_body / 2)
+        double w0 = W.qvel[da + 3], w1 = W.qvel[da + 4], w2 = W.qvel[da + 5];
+        double nrm = sqrt(w0 * w0 + w1 * w1 + w2 * w2);
+        double ax0 = 1, ax1 = 0, ax2 = 0;
+        if (nrm >= MJS_MINVAL) { ax0 = w0 / nrm; ax1 = w1 / nrm; ax2 = w2 / nrm; }
+        double ang = nrm * (double)h, sn, cs;
+        if (sizeof(real) == 8) sincos(0.5 * ang, &sn, &cs);
+        else { float fs, fc; sincosf((float)(0.5 * ang), &fs, &fc); sn = fs; cs = fc; }
+        double dq[4] = {cs, ax0 * sn, ax1 * sn, ax2 * sn};
+        double q[4] = {W.qpos[qa + 3], W.qpos[qa + 4], W.qpos[qa + 5], W.qpos[qa + 6]}, r[4];
+        quat_mul<double>(r, q, dq);
+        double n2 = 1.0 / sqrt(r[0] * r[0] + r[1] * r[1] + r[2] * r[2] + r[3] * r[3]);
+        W.qpos[qa + 3] = r[0] * n2; W.qpos[qa + 4] = r[1] * n2; W.qpos[qa + 5] = r[2] * n2; W.qpos[qa + 6] = r[3] * n2;
+      }
+    }
+    time += (double)h;
+    __syncwarp();
+  }
+
+  // ------------------------------------------------ one physics substep (legacy_step)
+  struct SubOut { real touch; int niter; };
+
+  // mj_step1 for the current (qpos, qvel): everything up to the constraint rows
+  __device__ static bool step1(const AM& A, WM& W, int lane, ConReg& C) {
+    kinematics(A, W, lane);
+    bool clamped = dynamics(A, W, lane);
+    collide(A, W, lane);
+    make_rows(A, W, lane, C);
+    return clamped;
+  }
+  // mj_step2: solve, sensor, integrate.  a_i = warm start in, qacc out.
+  __device__ static SubOut step2(const AM& A, WM& W, int lane, ConReg& C, bool clamped, real& a_i, double& time, bool do_integrate) {
+    SubOut o;
+    o.niter = solve(A, W, lane, C, a_i);
+    o.touch = touch_force(A, W, lane, C);
+    if (do_integrate) integrate(A, W, lane, clamped, time);
+    return o;
+  }
+};
+
+// ===================================================================== analytic UR IK
+// Device restatement of oracle/mjs_oracle.cpp ur_ik_all / ur_ik_closest (which
+// restates ur_analytic_ik.ur5e.inverse_kinematics_closest, robot.py:31-38).
+// Lane s (0..7) evaluates branch (s1, s5, s3) = bits (4, 2, 1); double precision.
+__device__ inline void dh_T(double* T, double th, double dd, double a, double al) {
+  double st, ct, sa, ca;
+  sincos(th, &st, &ct);
+  sincos(al, &sa, &ca);
+  T[0] = ct; T[1] = -st * ca; T[2] = st * sa; T[3] = a * ct;
+  T[4] = st; T[5] = ct * ca; T[6] = -ct * sa; T[7] = a * st;
+  T[8] = 0; T[9] = sa; T[10] = ca; T[11] = dd;
+}
+__device__ inline void mul34(double* C, const double* A, const double* B) {  // rigid 3x4 products
+  double R[12];
+  for (int i = 0; i < 3; i++) {
+    for (int j = 0; j < 3; j++) R[4 * i + j] = A[4 * i] * B[j] + A[4 * i + 1] * B[4 + j] + A[4 * i + 2] * B[8 + j];
+    R[4 * i + 3] = A[4 * i] * B[3] + A[4 * i + 1] * B[7] + A[4 * i + 2] * B[11] + A[4 * i + 3];
+  }
+  for (int i = 0; i < 12; i++) C[i] = R[i];
+}
+__device__ inline void inv34(double* B, const double* A) {
+  double R[12] = {A[0], A[4], A[8], 0, A[1], A[5], A[9], 0, A[2], A[6], A[10], 0};
+  for (int i = 0; i < 3; i++) R[4 * i + 3] = -(R[4 * i] * A[3] + R[4 * i + 1] * A[7] + R[4 * i + 2] * A[11]);
+  for (int i = 0; i < 12; i++) B[i] = R[i];
+}
+#define MJS_PI 3.14159265358979323846
+
+// all 32 lanes call; returns true (warp-uniform) and q[6] (identical in all lanes) on success
+__device__ inline bool ur_ik_closest_warp(const double* dh, const double* T06, const double* seed, double* qout, int lane) {
+  double d1 = dh[0], a2 = dh[1], a3 = dh[2], d4 = dh[3], d5 = dh[4], d6 = dh[5];
+  double q[6] = {0, 0, 0, 0, 0, 0};
+  double dist = 1e300;
+  bool valid = lane < 8;
+  int s1 = (lane >> 2) & 1, s5 = (lane >> 1) & 1, s3 = lane & 1;
+  double p05[3] = {T06[3] - d6 * T06[2], T06[7] - d6 * T06[6], T06[11] - d6 * T06[10]};
+  double rxy = hypot(p05[0], p05[1]);
+  if (rxy < fabs(d4)) valid = false;
+  if (valid) {
+    double psi = atan2(p05[1], p05[0]), phi = acos(d4 / rxy);
+    double th1 = psi + (s1 == 0 ? phi : -phi) + MJS_PI / 2;
+    double T01[12], T10[12], T16[12];
+    dh_T(T01, th1, d1, 0, MJS_PI / 2);
+    inv34(T10, T01);
+    mul34(T16, T10, T06);
+    double c5 = T16[10];
+    if (fabs(c5) > 1) { if (fabs(c5) < 1 + 1e-9) c5 = c5 > 0 ? 1 : -1; else valid = false; }
+    if (valid) {
+      double th5 = (s5 == 0 ? 1 : -1) * acos(c5);
+      double sn5 = sin(th5), th6, th234;
+      if (fabs(sn5) < 1e-9) {
+        th6 = 0;
+        th234 = c5 < 0 ? atan2(-T16[4], -T16[0]) : atan2(T16[4], T16[0]);
+      } else {
+        th6 = atan2(-T16[9] / sn5, T16[8] / sn5);
+        th234 = atan2(T16[6] / -sn5, T16[2] / -sn5);
+      }
+      double T45[12], T56[12], T46[12], T64[12], T14[12];
+      dh_T(T45, th5, d5, 0, -MJS_PI / 2);
+      dh_T(T56, th6, d6, 0, 0);
+      mul34(T46, T45, T56);
+      inv34(T64, T46);
+      mul34(T14, T16, T64);
+      double x = T14[3], y = T14[7];
+      double c3 = (x * x + y * y - a2 * a2 - a3 * a3) / (2 * a2 * a3);
+      if (fabs(c3) > 1) { if (fabs(c3) < 1 + 1e-9) c3 = c3 > 0 ? 1 : -1; else valid = false; }
+      if (valid) {
+        double th3 = (s3 == 0 ? 1 : -1) * acos(c3);
+        double th2 = atan2(y, x) - atan2(a3 * sin(th3), a2 + a3 * cos(th3));
+        double th4 = th234 - th2 - th3;
+        q[0] = th1; q[1] = th2; q[2] = th3; q[3] = th4; q[4] = th5; q[5] = th6;
+        dist = 0;
+        for (int i = 0; i < 6; i++) {
+          double v = fmod(q[i] + MJS_PI, 2 * MJS_PI);
+          if (v < 0) v += 2 * MJS_PI;
+          v -= MJS_PI;
+          double bq = v, bd = fabs(v - seed[i]);
+          for (int w = -1; w <= 1; w += 2) {
+            double c = v + w * 2 * MJS_PI;
+            if (c >= -2 * MJS_PI && c <= 2 * MJS_PI && fabs(c - seed[i]) < bd) { bd = fabs(c - seed[i]); bq = c; }
+          }
+          q[i] = bq;
+          dist += bd * bd;
+        }
+      }
+    }
+  }
+  if (!valid) dist = 1e300;
+  // argmin with lowest-lane tie break (the oracle keeps the first strict minimum)
+  double best = dist;
+  int bl = lane;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    double od = __shfl_xor_sync(FULLMASK, best, o);
+    int ol = __shfl_xor_sync(FULLMASK, bl, o);
+    if (od < best || (od == best && ol < bl)) { best = od; bl = ol; }
+  }
+  for (int i = 0; i < 6; i++) qout[i] = __shfl_sync(FULLMASK, q[i], bl);
+  return best < 1e299;
+}
+
+// ===================================================================== state layout
+// Per-env AoS record in HBM: SD doubles + SI ints.  A warp streams its record
+// with lane-strided (coalesced) loads once per control step.
+template <int NOBJ>
+struct ArmLayout {
+  static constexpr int NV = ARM_NLINK + 6 * NOBJ, NQ = ARM_NLINK + 7 * NOBJ;
+  static constexpr int QPOS = 0, QVEL = QPOS + NQ, WARM = QVEL + NV, CTRL = WARM + NV, TIME = CTRL + 6, TARGET = TIME + 1;
+  static constexpr int Q0 = TARGET + 3, Q1 = Q0 + 6, T0 = Q1 + 6, OVR = T0 + 1, RET = OVR + 3, SD = RET + 1;
+  static constexpr int I_STEP = 0, I_TRAJ = 1, I_SWA = 2, I_SWP = 3, I_SWC = 4, I_STATUS = 5, I_EPISODE = 6, I_LEN = 7, SI = 8;
+};
+
+struct ArmIO {
+  double* sd;
+  int* si;
+  const float* actions;
+  float* obs;
+  float* reward;
+  unsigned char* flags;
+  float* final_obs;
+  double* stats;
+  const unsigned char* mask;
+  int N, autoreset;
+  unsigned long long seed;
+  unsigned int env_offset, step_index;
+};
+
+template <typename real, int NOBJ>
+struct ArmTask {
+  using E = ArmEngine<real, NOBJ>;
+  using WM = WarpMem<real, NOBJ>;
+  using AM = ArmModel<real>;
+  using L = ArmLayout<NOBJ>;
+  static constexpr int NV = L::NV, NQ = L::NQ;
+
+  // task-level registers (identical in all lanes unless noted)
+  struct TS {
+    double time, target[3], t0, ovr[3], ret, tq0, tq1;  // tq0/tq1: lane j < 6 holds waypoint j
+    int step, traj, swa, swp, swc, status, episode, len;
+  };
+
+  __device__ static double uniform(const ArmIO& io, unsigned genv, unsigned episode, unsigned purpose, unsigned idx, double lo, double hi) {
+    Philox4 r = philox4x32_10(genv, episode, purpose, idx >> 1, (uint32_t)io.seed, (uint32_t)(io.seed >> 32));
+    double u = (idx & 1) ? u53(r.v[2], r.v[3]) : u53(r.v[0], r.v[1]);
+    return lo + (hi - lo) * u;
+  }
+
+  __device__ static void load(const AM& A, WM& W, const ArmIO& io, int e, int lane, TS& T, real& a_i) {
+    const double* s = io.sd + (size_t)e * L::SD;
+    for (int k = lane; k < NQ; k += 32) W.qpos[k] = s[L::QPOS + k];
+    if (lane < NV) { W.qvel[lane] = s[L::QVEL + lane]; a_i = (real)s[L::WARM + lane]; } else a_i = 0;
+    if (lane < ARM_NLINK) { W.ctrl[lane] = s[L::CTRL + lane]; T.tq0 = s[L::Q0 + lane]; T.tq1 = s[L::Q1 + lane]; } else { T.tq0 = 0; T.tq1 = 0; }
+    T.time = s[L::TIME]; T.t0 = s[L::T0]; T.ret = s[L::RET];
+    for (int k = 0; k < 3; k++) { T.target[k] = s[L::TARGET + k]; T.ovr[k] = s[L::OVR + k]; }
+    const int* si = io.si + (size_t)e * L::SI;
+    T.step = si[L::I_STEP]; T.traj = si[L::I_TRAJ]; T.swa = si[L::I_SWA]; T.swp = si[L::I_SWP]; T.swc = si[L::I_SWC];
+    T.status = si[L::I_STATUS]; T.episode = si[L::I_EPISODE]; T.len = si[L::I_LEN];
+    if (lane == 0) W.status = 0;
+    init_static(A, W, lane, T);
+    __syncwarp();
+  }
+
+  __device__ static void init_static(const AM& A, WM& W, int lane, const TS& T) {
+    if (lane < 9) { W.xmat[SLOT_STATIC][lane] = (lane % 4 == 0) ? (real)1 : (real)0; W.xmat[SLOT_OVR][lane] = A.has_ovr ? A.ovr_mat[lane] : ((lane % 4 == 0) ? (real)1 : (real)0); }
+    if (lane < 3) { W.xpos[SLOT_STATIC][lane] = 0; W.xpos[SLOT_OVR][lane] = (real)T.ovr[lane]; }
+  }
+
+  __device__ static void store(WM& W, const ArmIO& io, int e, int lane, const TS& T, real a_i) {
+    double* s = io.sd + (size_t)e * L::SD;
+    __syncwarp();
+    for (int k = lane; k < NQ; k += 32) s[L::QPOS + k] = W.qpos[k];
+    if (lane < NV) { s[L::QVEL + lane] = W.qvel[lane]; s[L::WARM + lane] = (double)a_i; }
+    if (lane < ARM_NLINK) { s[L::CTRL + lane] = W.ctrl[lane]; s[L::Q0 + lane] = T.tq0; s[L::Q1 + lane] = T.tq1; }
+    if (lane == 0) {
+      s[L::TIME] = T.time; s[L::T0] = T.t0; s[L::RET] = T.ret;
+      for (int k = 0; k < 3; k++) { s[L::TARGET + k] = T.target[k]; s[L::OVR + k] = T.ovr[k]; }
+      int* si = io.si + (size_t)e * L::SI;
+      si[L::I_STEP] = T.step; si[L::I_TRAJ] = T.traj; si[L::I_SWA] = T.swa; si[L::I_SWP] = T.swp; si[L::I_SWC] = T.swc;
+      si[L::I_STATUS] = T.status | W.status; si[L::I_EPISODE] = T.episode; si[L::I_LEN] = T.len;
+    }
+  }
+
+  // robot.py:218-259 servoL / servoJ.  tcp == nullptr: joint target in qt (lane j holds qt_j in all lanes' array)
+  __device__ static void servoJ(WM& W, int lane, TS& T, const double* qt) {
+    if (lane < ARM_NLINK) { T.tq0 = W.qpos[lane]; T.tq1 = qt[lane]; }
+    T.t0 = T.time;
+    T.traj = 1;
+  }
+  __device__ static bool tcp_to_joints(const AM& A, const double* tcp, const double* seed, double* q, int lane) {
+    // top-down flange pose (TOP_DOWN_QUATERNION = 180 deg about x), robot.py:138-151
+    double T06[12] = {1, 0, 0, tcp[0] - (double)A.tcp_offset[0], 0, -1, 0, tcp[1] + (double)A.tcp_offset[1], 0, 0, -1, tcp[2] + (double)A.tcp_offset[2]};
+    return ur_ik_closest_warp(A.ik_dh, T06, seed, q, lane);
+  }
+  __device__ static void servoL(const AM& A, WM& W, int lane, TS& T, const double* tcp) {
+    double seed[6], q[6];
+    for (int i = 0; i < 6; i++) seed[i] = W.qpos[i];
+    if (!tcp_to_joints(A, tcp, seed, q, lane)) { T.status |= MJS_STATUS_IK_FAIL; return; }
+    servoJ(W, lane, T, q);
+  }
+  // joint_trajectory.py:33-47 + robot.py:261-272
+  __device__ static void before_substep(const AM& A, WM& W, int lane, const TS& T) {
+    if (T.traj && lane < ARM_NLINK) {
+      double t0 = T.t0, t1 = T.t0 + A.control_dt;
+      double tt = fmin(fmax(T.time, t0), t1);
+      W.ctrl[lane] = T.tq0 + (T.tq1 - T.tq0) * (tt - t0) / (t1 - t0);
+    }
+    __syncwarp();
+  }
+  __device__ static void switch_update(const AM& A, TS& T, real force) {
+    int was = T.swp;  // switch.py:51-60
+    T.swp = ((double)force >= A.touch_lo && (double)force <= A.touch_hi) ? 1 : 0;
+    if (T.swp && !was) T.swa = !T.swa;
+    T.swc += T.swp;
+  }
+
+  __device__ static void tcp_position(const AM& A, const WM& W, double* tcp) {
+    const real* R = W.xmat[A.tcp_slot];
+    real v[3], sm[9], o[3];
+    real tp[3] = {A.tcp_pos[0], A.tcp_pos[1], A.tcp_pos[2]}, off[3] = {A.tcp_offset[0], A.tcp_offset[1], A.tcp_offset[2]};
+    mat_vec(v, R, tp);
+    for (int r = 0; r < 3; r++)
+      for (int c = 0; c < 3; c++) sm[3 * r + c] = R[3 * r] * A.tcp_mat[c] + R[3 * r + 1] * A.tcp_mat[3 + c] + R[3 * r + 2] * A.tcp_mat[6 + c];
+    mat_vec(o, sm, off);
+    for (int k = 0; k < 3; k++) tcp[k] = (double)W.xpos[A.tcp_slot][k] + (double)v[k] + (double)o[k];
+  }
+
+  struct Out { double obs[16]; double reward; int terminated, truncated, success, done; };
+
+  // observation + reward + termination of the CURRENT state (kinematics must be fresh)
+  __device__ static void observe(const AM& A, const WM& W, const TS& T, Out& o) {
+    double tcp[3];
+    tcp_position(A, W, tcp);
+    bool accomplished = false, has_success = false;
+    double reward = 0;
+    for (int k = 0; k < 16; k++) o.obs[k] = 0;
+    if (A.kind == MJS_TASK_REACH) {
+      for (int k = 0; k < 3; k++) { o.obs[k] = tcp[k]; o.obs[3 + k] = T.target[k]; }
+      double dist = sqrt((tcp[0] - T.target[0]) * (tcp[0] - T.target[0]) + (tcp[1] - T.target[1]) * (tcp[1] - T.target[1]) + (tcp[2] - T.target[2]) * (tcp[2] - T.target[2]));
+      reward = A.reward_type == 0 ? (dist < A.goal_threshold ? 1.0 : 0.0) : -dist;
+    } else if (A.kind == MJS_TASK_PUSH) {
+      for (int k = 0; k < 3; k++) o.obs[k] = tcp[k];
+      o.obs[3] = T.target[0]; o.obs[4] = T.target[1];
+      double sum = 0, nearest = 1e300;
+      int within = 0;
+      for (int b = 0; b < NOBJ; b++) {
+        double x = W.qpos[ARM_NLINK + 7 * b], y = W.qpos[ARM_NLINK + 7 * b + 1];
+        o.obs[5 + 2 * b] = x; o.obs[6 + 2 * b] = y;
+        double dd = hypot(x - T.target[0], y - T.target[1]);
+        sum += dd;
+        if (dd < A.target_radius) within++;
+        nearest = fmin(nearest, hypot(tcp[0] - x, tcp[1] - y));
+      }
+      if (A.reward_type == 0) reward = within;
+      else reward = (-sum / NOBJ - A.nearest_coef * nearest) * 0.1;
+      accomplished = within == NOBJ;
+    } else {  // BUTTON
+      for (int k = 0; k < 6; k++) o.obs[k] = W.qpos[k];
+      const real* R = W.xmat[A.touch_slot];
+      real tp[3] = {A.touch_pos[0], A.touch_pos[1], A.touch_pos[2]}, v[3];
+      mat_vec(v, R, tp);
+      double quirk = 0.5 * ((double)A.touch_size[0] / 1.01);  // switch.py:86-87
+      for (int k = 0; k < 3; k++) o.obs[6 + k] = (double)W.xpos[A.touch_slot][k] + (double)v[k] + quirk;
+      o.obs[9] = T.swa;
+      double dg = sqrt((tcp[0] - A.button_goal[0]) * (tcp[0] - A.button_goal[0]) + (tcp[1] - A.button_goal[1]) * (tcp[1] - A.button_goal[1]) + (tcp[2] - A.button_goal[2]) * (tcp[2] - A.button_goal[2]));
+      bool goal = T.swa && dg < A.button_goal_radius;
+      reward = goal ? 1.0 : 0.0;
+      accomplished = goal; has_success = true;
+    }
+    bool terminate = accomplished;
+    if (A.kind == MJS_TASK_PUSH && A.max_steps > 0 && T.step >= A.max_steps) terminate = true;
+    bool timeup = A.time_limit > 0 && T.time >= A.time_limit;
+    double discount = (accomplished && A.kind != MJS_TASK_REACH) ? 0.0 : 1.0;
+    bool last = terminate || timeup;
+    o.reward = reward;
+    o.done = last; o.truncated = last && discount > 0; o.terminated = last && discount == 0;
+    o.success = has_success ? (accomplished ? 1 : 0) : 0;
+  }
+
+  // One control step for the env owned by this warp (composer loop)
+  __device__ static void control_step(const AM& A, WM& W, int lane, TS& T, real& a_i, const double* action, Out& o) {
+    typename E::ConReg C;
+    if (A.kind == MJS_TASK_REACH) servoL(A, W, lane, T, action);
+    else if (A.kind == MJS_TASK_PUSH) {
+      T.step += 1;
+      double tcp[3] = {action[0], action[1], A.tcp_z};
+      servoL(A, W, lane, T, tcp);
+    } else {
+      if (A.action_dim == 7) servoJ(W, lane, T, action);
+      else servoL(A, W, lane, T, action);
+    }
+    for (int k = 0; k < A.n_sub; k++) {
+      before_substep(A, W, lane, T);
+      bool clamped = E::step1(A, W, lane, C);
+      typename E::SubOut so = E::step2(A, W, lane, C, clamped, a_i, T.time, true);
+      if (A.kind == MJS_TASK_BUTTON) switch_update(A, T, so.touch);
+    }
+    E::kinematics(A, W, lane);
+    observe(A, W, T, o);
+    T.ret += o.reward;
+    T.len += 1;
+    bool bad = false;
+    if (lane < NV) bad = !(isfinite(W.qvel[lane]) && isfinite(W.qpos[lane]));
+    if (__any_sync(FULLMASK, bad)) { T.status |= MJS_STATUS_NAN; o.done = 1; o.truncated = 1; o.terminated = 0; }
+  }
+
+  // Episode reset: sample boxes, IK, mj_forward, settle (Planar Push)
+  __device__ static void reset_env(const AM& A, WM& W, int lane, const ArmIO& io, int e, TS& T, real& a_i, Out& o) {
+    unsigned genv = io.env_offset + e;
+    T.episode += 1;
+    unsigned ep = (unsigned)T.episode;
+    unsigned idx = 0;
+    double spawn[3], q[6], seed[6] = {0, 0, 0, 0, 0, 0};
+    for (int k = 0; k < 3; k++) spawn[k] = uniform(io, genv, ep, MJS_RNG_RESET, idx++, A.spawn_lo[k], A.spawn_hi[k]);
+    bool ok = tcp_to_joints(A, spawn, seed, q, lane);
+    if (!ok) for (int k = 0; k < 6; k++) q[k] = 0;  // robot.py:179-183: unreachable reset pose is ignored
+    for (int k = 0; k < 3; k++) T.target[k] = uniform(io, genv, ep, MJS_RNG_RESET, idx++, A.target_lo[k], A.target_hi[k]);
+    if (A.kind == MJS_TASK_BUTTON) { for (int k = 0; k < 3; k++) { T.ovr[k] = T.target[k]; T.target[k] = 0; } }
+    if (lane < ARM_NLINK) { W.qpos[lane] = q[lane]; W.ctrl[lane] = q[lane]; }
+    if (lane < NV) W.qvel[lane] = 0;
+    if (NOBJ > 0) {
+      // robot_planar_push.py:169-176 with a conservative overlap test: resample ALL props
+      // until no two props and no prop/pusher overlap in the xy-plane (superset of ncon > 0)
+      double px[NOBJ > 0 ? NOBJ : 1], py[NOBJ > 0 ? NOBJ : 1], pz[NOBJ > 0 ? NOBJ : 1];
+      for (int attempt = 0; attempt < 64; attempt++) {
+        for (int b = 0; b < NOBJ; b++) {
+          px[b] = uniform(io, genv, ep, MJS_RNG_RESET, idx++, A.obj_lo[0], A.obj_hi[0]);
+          py[b] = uniform(io, genv, ep, MJS_RNG_RESET, idx++, A.obj_lo[1], A.obj_hi[1]);
+          pz[b] = uniform(io, genv, ep, MJS_RNG_RESET, idx++, A.obj_lo[2], A.obj_hi[2]);
+        }
+        bool coll = false;
+        double dmin = 2 * A.obj_radius;
+        for (int b = 0; b < NOBJ; b++) {
+          if (hypot(px[b] - spawn[0], py[b] - spawn[1]) < dmin) coll = true;
+          for (int c = 0; c < b; c++) if (hypot(px[b] - px[c], py[b] - py[c]) < dmin) coll = true;
+        }
+        if (!coll) break;
+      }
+      if (lane < NOBJ) {
+        int qa = ARM_NLINK + 7 * lane;
+        W.qpos[qa] = px[lane]; W.qpos[qa + 1] = py[lane]; W.qpos[qa + 2] = pz[lane];
+        W.qpos[qa + 3] = 1; W.qpos[qa + 4] = 0; W.qpos[qa + 5] = 0; W.qpos[qa + 6] = 0;
+      }
+    }
+    T.time = 0; T.t0 = 0; T.traj = 0; T.step = 0; T.ret = 0; T.len = 0; T.tq0 = 0; T.tq1 = 0;
+    T.swa = 0; T.swc = 0;  // Switch.initialize_episode keeps _is_pressed (switch.py:62-65)
+    a_i = 0;
+    init_static(A, W, lane, T);
+    __syncwarp();
+    // mj_forward at the reset state (actuator force is zero: ctrl == qpos, qvel == 0)
+    typename E::ConReg C;
+    bool clamped = E::step1(A, W, lane, C);
+    typename E::SubOut so = E::step2(A, W, lane, C, clamped, a_i, T.time, false);
+    for (int k = 0; k < A.settle_steps; k++) {
+      E::step2(A, W, lane, C, clamped, a_i, T.time, true);  // re-solve + integrate (mj_step2)
+      clamped = E::step1(A, W, lane, C);                      // mj_step1
+      so.touch = 0;
+    }
+    if (A.settle_steps > 0) { E::kinematics(A, W, lane); }
+    if (A.kind == MJS_TASK_BUTTON) switch_update(A, T, so.touch);
+    observe(A, W, T, o);
+  }
+};
+
+// ========================================================================= kernels
+template <typename real, int NOBJ>
+__device__ __forceinline__ void arm_write_out(const ArmModel<real>& A, const ArmIO& io, int e, int lane,
+                                              const typename ArmTask<real, NOBJ>::Out& o, bool write_flags) {
+  int O = A.obs_dim;
+  if (io.obs && lane < O) {
+    double v = 0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) if (k == lane) v = o.obs[k];
+    io.obs[(size_t)e * O + lane] = (float)v;
+  }
+  if (write_flags && lane == 0) {
+    if (io.reward) io.reward[e] = (float)o.reward;
+    if (io.flags) reinterpret_cast<uchar4*>(io.flags)[e] = make_uchar4(o.terminated, o.truncated, o.success, o.done);
+  }
+}
+
+template <typename real, int NOBJ, int WPB>
+__global__ void __launch_bounds__(WPB * 32) arm_step_kernel(const __grid_constant__ ArmModel<real> A, ArmIO io) {
+  using TK = ArmTask<real, NOBJ>;
+  using WM = WarpMem<real, NOBJ>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WM* wm = reinterpret_cast<WM*>(smem_raw);
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int e = blockIdx.x * WPB + warp;
+  if (e >= io.N) return;
+  WM& W = wm[warp];
+  typename TK::TS T;
+  real a_i;
+  TK::load(A, W, io, e, lane, T, a_i);
+  // action (all lanes hold the full vector)
+  double action[8];
+  int AD = A.action_dim;
+  if (io.actions) {
+    for (int k = 0; k < 8; k++) action[k] = k < AD ? (double)io.actions[(size_t)e * AD + k] : 0.0;
+  } else {
+    unsigned genv = io.env_offset + e;
+    for (int k = 0; k < 8; k++) {
+      action[k] = 0;
+      if (k < AD) {
+        Philox4 r = philox4x32_10(genv, io.step_index, MJS_RNG_ACTION, k >> 1, (uint32_t)io.seed, (uint32_t)(io.seed >> 32));
+        double u = (k & 1) ? u53(r.v[2], r.v[3]) : u53(r.v[0], r.v[1]);
+        action[k] = A.action_lo[k] + (A.action_hi[k] - A.action_lo[k]) * u;
+        if (A.kind == MJS_TASK_BUTTON && k < 6) action[k] = fmin(fmax(W.qpos[k] + action[k], -3.14), 3.14);
+      }
+    }
+  }
+  typename TK::Out o;
+  TK::control_step(A, W, lane, T, a_i, action, o);
+  if (io.final_obs && lane < A.obs_dim) {
+    double v = 0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) if (k == lane) v = o.obs[k];
+    io.final_obs[(size_t)e * A.obs_dim + lane] = (float)v;
+  }
+  if (lane == 0) {
+    if (io.reward) io.reward[e] = (float)o.reward;
+    if (io.flags) reinterpret_cast<uchar4*>(io.flags)[e] = make_uchar4(o.terminated, o.truncated, o.success, o.done);
+    if (o.done && io.stats) {
+      atomicAdd(io.stats + 0, T.ret); atomicAdd(io.stats + 1, (double)T.len); atomicAdd(io.stats + 2, 1.0);
+      atomicAdd(io.stats + 3, (double)o.success); atomicAdd(io.stats + 4, (double)o.truncated);
+      atomicAdd(io.stats + 5, (T.status | W.status) ? 1.0 : 0.0);
+    }
+  }
+  if (o.done && io.autoreset) {
+    typename TK::Out o2;
+    T.status |= W.status;
+    TK::reset_env(A, W, lane, io, e, T, a_i, o2);
+    arm_write_out<real, NOBJ>(A, io, e, lane, o2, false);
+  } else {
+    arm_write_out<real, NOBJ>(A, io, e, lane, o, false);
+  }
+  TK::store(W, io, e, lane, T, a_i);
+}
+
+template <typename real, int NOBJ, int WPB>
+__global__ void __launch_bounds__(WPB * 32) arm_reset_kernel(const __grid_constant__ ArmModel<real> A, ArmIO io) {
+  using TK = ArmTask<real, NOBJ>;
+  using WM = WarpMem<real, NOBJ>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WM* wm = reinterpret_cast<WM*>(smem_raw);
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int e = blockIdx.x * WPB + warp;
+  if (e >= io.N) return;
+  if (io.mask && !io.mask[e]) return;
+  WM& W = wm[warp];
+  typename TK::TS T;
+  real a_i;
+  TK::load(A, W, io, e, lane, T, a_i);
+  typename TK::Out o;
+  TK::reset_env(A, W, lane, io, e, T, a_i, o);
+  arm_write_out<real, NOBJ>(A, io, e, lane, o, false);
+  TK::store(W, io, e, lane, T, a_i);
+}
+
+// mj_forward on injected states (mjs_set_state with forward != 0): refresh the warm start
+template <typename real, int NOBJ, int WPB>
+__global__ void __launch_bounds__(WPB * 32) arm_forward_kernel(const __grid_constant__ ArmModel<real> A, ArmIO io, int first, int count) {
+  using TK = ArmTask<real, NOBJ>;
+  using E = ArmEngine<real, NOBJ>;
+  using WM = WarpMem<real, NOBJ>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WM* wm = reinterpret_cast<WM*>(smem_raw);
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int e = first + blockIdx.x * WPB + warp;
+  if (e >= first + count || e >= io.N) return;
+  WM& W = wm[warp];
+  typename TK::TS T;
+  real a_i;
+  TK::load(A, W, io, e, lane, T, a_i);
+  typename E::ConReg C;
+  bool clamped = E::step1(A, W, lane, C);
+  E::step2(A, W, lane, C, clamped, a_i, T.time, false);
+  TK::store(W, io, e, lane, T, a_i);
+}
+
+// debug: run mj_forward for one env and dump intermediate stages (tests only)
+//   out: [0..35] Marm, [36..36+NV) fsm, [..+NV) qacc, [..+NV) fcon, then ncon, then per contact (dist,pos3,normal3) x ncon, then link xpos (18), S (36)
+template <typename real, int NOBJ, int WPB>
+__global__ void __launch_bounds__(WPB * 32) arm_debug_kernel(const __grid_constant__ ArmModel<real> A, ArmIO io, int env, double* out) {
+  using TK = ArmTask<real, NOBJ>;
+  using E = ArmEngine<real, NOBJ>;
+  using WM = WarpMem<real, NOBJ>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WM* wm = reinterpret_cast<WM*>(smem_raw);
+  int lane = threadIdx.x & 31;
+  if (threadIdx.x >= 32) return;
+  WM& W = wm[0];
+  typename TK::TS T;
+  real a_i;
+  TK::load(A, W, io, env, lane, T, a_i);
+  typename E::ConReg C;
+  bool clamped = E::step1(A, W, lane, C);
+  typename E::SubOut so = E::step2(A, W, lane, C, clamped, a_i, T.time, false);
+  __syncwarp();
+  constexpr int NV = WM::NV;
+  if (lane == 0) {
+    int p = 0;
+    for (int i = 0; i < 6; i++) for (int j = 0; j < 6; j++) out[p++] = W.Marm[i][j];
+    for (int i = 0; i < NV; i++) out[p++] = W.fsm[i];
+    for (int i = 0; i < NV; i++) out[p++] = W.a[i];
+    for (int i = 0; i < NV; i++) out[p++] = W.fcon[i];
+    out[p++] = W.ncon;
+    out[p++] = so.niter;
+    out[p++] = so.touch;
+    for (int c = 0; c < ARM_MAXC; c++) for (int k = 0; k < 7; k++) out[p++] = c < W.ncon ? (double)W.craw[k][c] : 0.0;
+    for (int i = 0; i < 6; i++) for (int k = 0; k < 3; k++) out[p++] = W.xpos[SLOT_LINK0 + i][k];
+    for (int i = 0; i < 6; i++) for (int k = 0; k < 6; k++) out[p++] = W.S[i][k];
+    for (int c = 0; c < ARM_MAXC; c++) for (int k = 0; k < 4; k++) out[p++] = c < W.ncon ? (double)W.cf[k][c] : 0.0;
+  }
+}

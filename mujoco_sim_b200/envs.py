@@ -22,6 +22,9 @@ from .model.cstruct import MjsEnvState
 
 _BUILDERS = {
     "point_mass_reach": _tasks.build_pointmass_reach,
+    "robot_reach": _tasks.build_robot_reach,
+    "robot_planar_push": _tasks.build_planar_push,
+    "robot_push_button": _tasks.build_push_button,
 }
 
 
@@ -147,9 +150,6 @@ class BatchedMujocoSimEnv:
         p = ctypes.c_void_p()
         _lib.check(self._L.mjs_stats_device(self._h, ctypes.byref(p)))
         # wrap without copying
-        import torch.utils.dlpack  # noqa: F401
-        from torch import frombuffer  # noqa: F401
-        buf = (ctypes.c_double * 8).from_address(0) if False else None  # pragma: no cover
         return _wrap_device_f64(p.value, 8, self.device)
 
     @property

@@ -121,3 +121,220 @@ def build_pointmass_reach(reward_type: str = DENSE_BIASED_NEG_DISTANCE_REWARD, m
         np.array([0.05, 0.05], np.float32),
         np.float32,
     )
+
+
+# =====================================================================  UR5e arm
+# Collision filtering bits (DESIGN.md "collision scope"): the arm's link geoms
+# only collide with the ground plane; pusher / fingertip / props collide with
+# each other and the plane.  MuJoCo's defaults would also test arm x prop and
+# non-adjacent arm x arm pairs, which never touch in these workspaces.
+_BIT_WORLD = 1
+_BIT_ARM = 2
+
+
+def _ur5e(world: S.Body):
+    """UR5e kinematic tree restated from mujoco_menagerie universal_robots_ur5e/ur5e.xml
+    [UPSTREAM-RECALL, file not in this image; SURVEY.md App. A.2] with the reference's
+    edits: gravcomp=1 on every body (robot.py:81-82) and the base quaternion
+    overwritten to (0,0,0,-1) (robot.py:320).  Returns (wrist_3 body, actuators)."""
+    J = dict(armature=0.1)
+    full = (-6.28319, 6.28319)
+    col = dict(contype=_BIT_ARM, conaffinity=0)
+
+    def cap(size, pos, quat=(1, 0, 0, 0), name=""):
+        return S.Geom(S.CAPSULE, size, pos=pos, quat=quat, name=name, **col)
+
+    base = world.add(S.Body("ur5e/base", quat=(0, 0, 0, -1), gravcomp=1.0,
+                            inertial=S.Inertial(4.0, diaginertia=(0.00443333156, 0.00443333156, 0.0072))))
+    sh = base.add(S.Body("ur5e/shoulder_link", pos=(0, 0, 0.163), gravcomp=1.0,
+                         inertial=S.Inertial(3.7, diaginertia=(0.0102675, 0.0102675, 0.00666))))
+    sh.joints.append(S.Joint(S.HINGE, axis=(0, 0, 1), range=full, name="ur5e/shoulder_pan_joint", **J))
+    sh.geoms.append(cap((0.06, 0.06), (0, 0, -0.04), name="ur5e/shoulder_col"))
+    ua = sh.add(S.Body("ur5e/upper_arm_link", pos=(0, 0.138, 0), quat=(1, 0, 1, 0), gravcomp=1.0,
+                       inertial=S.Inertial(8.393, pos=(0, 0, 0.2125), diaginertia=(0.133886, 0.133886, 0.0151074))))
+    ua.joints.append(S.Joint(S.HINGE, axis=(0, 1, 0), range=full, name="ur5e/shoulder_lift_joint", **J))
+    ua.geoms.append(cap((0.06, 0.06), (0, -0.04, 0), (1, 1, 0, 0), name="ur5e/upper_col0"))
+    ua.geoms.append(cap((0.05, 0.2), (0, 0, 0.2), name="ur5e/upper_col1"))
+    fa = ua.add(S.Body("ur5e/forearm_link", pos=(0, -0.131, 0.425), gravcomp=1.0,
+                       inertial=S.Inertial(2.275, pos=(0, 0, 0.196), diaginertia=(0.0311796, 0.0311796, 0.004095))))
+    fa.joints.append(S.Joint(S.HINGE, axis=(0, 1, 0), range=(-3.1415, 3.1415), name="ur5e/elbow_joint", **J))
+    fa.geoms.append(cap((0.055, 0.06), (0, 0.08, 0), (1, 1, 0, 0), name="ur5e/fore_col0"))
+    fa.geoms.append(cap((0.038, 0.19), (0, 0, 0.2), name="ur5e/fore_col1"))
+    w1 = fa.add(S.Body("ur5e/wrist_1_link", pos=(0, 0, 0.392), quat=(1, 0, 1, 0), gravcomp=1.0,
+                       inertial=S.Inertial(1.219, pos=(0, 0.127, 0), diaginertia=(0.0025599, 0.0025599, 0.0021942))))
+    w1.joints.append(S.Joint(S.HINGE, axis=(0, 1, 0), range=full, name="ur5e/wrist_1_joint", **J))
+    w1.geoms.append(cap((0.04, 0.07), (0, 0.05, 0), (1, 1, 0, 0), name="ur5e/w1_col"))
+    w2 = w1.add(S.Body("ur5e/wrist_2_link", pos=(0, 0.127, 0), gravcomp=1.0,
+                       inertial=S.Inertial(1.219, pos=(0, 0, 0.1), diaginertia=(0.0025599, 0.0025599, 0.0021942))))
+    w2.joints.append(S.Joint(S.HINGE, axis=(0, 0, 1), range=full, name="ur5e/wrist_2_joint", **J))
+    w2.geoms.append(cap((0.04, 0.06), (0, 0, 0.04), name="ur5e/w2_col0"))
+    w2.geoms.append(cap((0.04, 0.04), (0, 0.02, 0.1), (1, 1, 0, 0), name="ur5e/w2_col1"))
+    w3 = w2.add(S.Body("ur5e/wrist_3_link", pos=(0, 0, 0.1), gravcomp=1.0,
+                       inertial=S.Inertial(0.1889, pos=(0, 0.0771683, 0), quat=(1, 0, 0, 1),
+                                           diaginertia=(0.000132134, 9.90863e-05, 9.90863e-05))))
+    w3.joints.append(S.Joint(S.HINGE, axis=(0, 1, 0), range=full, name="ur5e/wrist_3_joint", **J))
+    w3.geoms.append(S.Geom(S.CYLINDER, (0.04, 0.02), pos=(0, 0.08, 0), quat=(1, 1, 0, 0), name="ur5e/w3_col", **col))
+    w3.sites.append(S.Site("ur5e/attachment_site", pos=(0, 0.1, 0), quat=(-1, 1, 0, 0)))
+    names = ["shoulder_pan", "shoulder_lift", "elbow", "wrist_1", "wrist_2", "wrist_3"]
+    acts = []
+    for i, n in enumerate(names):
+        big = i < 3
+        cr = (-3.1415, 3.1415) if n == "elbow" else (-6.2831, 6.2831)
+        acts.append(S.PositionActuator(f"ur5e/{n}_joint", kp=2000.0 if big else 500.0, kv=400.0 if big else 100.0,
+                                       ctrlrange=cr, forcerange=(-150.0, 150.0) if big else (-28.0, 28.0)))
+    return w3, acts
+
+
+def _arena_plane(world: S.Body, side=3.0):
+    # EmptyRobotArena(3): one ground plane (empty_robot_arena.py:18-20)
+    world.geoms.append(S.Geom(S.PLANE, (side / 2, side / 2, 0.1), name="ground", contype=_BIT_WORLD, conaffinity=_BIT_WORLD | _BIT_ARM))
+
+
+def _robot_task_common(t: MjsTask, comp: Compiled, control_dt, physics_dt, tcp_offset):
+    t.n_sub = int(round(control_dt / physics_dt))
+    t.control_dt = control_dt
+    t.tcp_site = comp.site_id["ur5e/attachment_site"]
+    t.arm_qadr = comp.jnt_qadr["ur5e/shoulder_pan_joint"]
+    t.set("tcp_offset", tcp_offset)
+    t.set("ik_dh", UR5E_DH)
+
+
+@dataclasses.dataclass
+class RobotPushConfig:
+    """Mirror of robot_planar_push.py:29-73 (state observations only) plus the
+    `object_type` switch of SURVEY.md D2: the measured config uses cylinders."""
+
+    reward_type: str = DENSE_NEG_DISTANCE_REWARD
+    physics_timestep: float = 0.005
+    control_timestep: float = 0.1
+    max_control_steps_per_episode: int = 500
+    nearest_object_reward_coefficient: float = 0.1
+    target_radius: float = 0.05
+    n_objects: int = 3
+    object_type: str = "cylinder"
+
+
+def build_planar_push(config: RobotPushConfig | None = None) -> TaskBundle:
+    """RobotPushTask scene (robot_planar_push.py:76-176, eef/cylinder.py:18-41) with
+    CylinderProp objects (r 0.02, half-height 0.019, mass 0.1, condim 4,
+    friction [1, 0.05, 0] -- google_block.py:31,43-49 on a primitive)."""
+    cfg = config or RobotPushConfig()
+    assert cfg.object_type == "cylinder", "convex-hull google blocks are SURVEY.md 8f-1 (not built)"
+    assert 1 <= cfg.n_objects <= 4, "nv = 6 + 6*n_objects must stay <= 32"
+    world = S.Body("world")
+    _arena_plane(world)
+    w3, acts = _ur5e(world)
+    eef = w3.add(S.Body("ur5e/cylinder_eef", pos=(0, 0.1, 0), quat=(-1, 1, 0, 0)))
+    eef.geoms.append(S.Geom(S.CYLINDER, (0.02, 0.05), pos=(0, 0, 0.051), mass=0.1, name="cylinder-EEF"))
+    R, H = 0.02, 0.019
+    for i in range(cfg.n_objects):
+        ob = world.add(S.Body(f"object{i}", pos=(-0.1 + 0.1 * i, -0.45, H)))
+        ob.joints.append(S.Joint(S.FREE, name=f"object{i}/free"))
+        ob.geoms.append(S.Geom(S.CYLINDER, (R, H), mass=0.1, condim=4, friction=(1.0, 0.05, 0.0), name=f"object{i}/geom"))
+    sc = S.Scene(world, actuators=acts, timestep=cfg.physics_timestep, integrator=1)
+    comp = compile_scene(sc)
+    t = MjsTask()
+    t.kind = MACROS["MJS_TASK_PUSH"]
+    _robot_task_common(t, comp, cfg.control_timestep, cfg.physics_timestep, (0, 0, 0.1))
+    t.reward_type = 0 if cfg.reward_type == SPARSE_REWARD else 1
+    t.max_steps = cfg.max_control_steps_per_episode
+    t.n_obj = cfg.n_objects
+    t.action_dim = 2
+    t.obs_dim = 5 + 2 * cfg.n_objects
+    for i in range(cfg.n_objects):
+        t.obj_body[i] = comp.body_id[f"object{i}"]
+        t.obj_qadr[i] = comp.jnt_qadr[f"object{i}/free"]
+        t.obj_dadr[i] = comp.jnt_dadr[f"object{i}/free"]
+    t.time_limit = 0.0  # scripts build Environment without time_limit (scripts/sb3/planar_push.py:72-73)
+    t.target_radius = cfg.target_radius
+    t.nearest_coef = cfg.nearest_object_reward_coefficient
+    t.tcp_z = 0.02
+    t.obj_radius = R
+    t.settle_steps = 150
+    t.set("spawn_lo", (-0.2, -0.6, 0.02)); t.set("spawn_hi", (0.2, -0.3, 0.02))
+    t.set("target_lo", (-0.15, -0.55, 0.001)); t.set("target_hi", (0.15, -0.35, 0.005))
+    t.set("obj_lo", (-0.15, -0.55, 0.05)); t.set("obj_hi", (0.15, -0.35, 0.2))
+    # action_spec is [-1,1]^2 (robot_planar_push.py:229-234); synthetic rollouts draw from the
+    # reachable robot workspace instead (SURVEY.md 8d) because servoL raises outside it
+    t.set("action_lo", [-0.2, -0.6]); t.set("action_hi", [0.2, -0.3])
+    keys = [("ur5e/tcp_position", 3), ("target_position", 2), ("block_positions", 2 * cfg.n_objects)]
+    return TaskBundle("robot_planar_push", comp, t, keys, np.array([-1, -1], np.float32), np.array([1, 1], np.float32), np.float32)
+
+
+def _rigid_gripper(w3: S.Body):
+    """Rigid stand-in for the Robotiq 2F-85: the menagerie MJCF is not
+    obtainable here.  Same TCP offset 0.174 (gripper.py:44-48) and ~0.9 kg; a capsule
+    palm that only touches the ground plane plus a spherical fingertip at the TCP."""
+    g = w3.add(S.Body("ur5e/gripper", pos=(0, 0.1, 0), quat=(-1, 1, 0, 0),
+                      inertial=S.Inertial(0.9, pos=(0, 0, 0.06), diaginertia=(0.002, 0.002, 0.0008))))
+    g.geoms.append(S.Geom(S.CAPSULE, (0.03, 0.05), pos=(0, 0, 0.075), contype=_BIT_ARM, conaffinity=0, name="gripper/palm"))
+    g.geoms.append(S.Geom(S.SPHERE, (0.015,), pos=(0, 0, 0.159), name="gripper/fingertip"))
+    return g
+
+
+@dataclasses.dataclass
+class RobotReachConfig:
+    """Mirror of robot_reach.py:33-82 (state observations, ABS_EEF_ACTION)."""
+
+    reward_type: str = DENSE_NEG_DISTANCE_REWARD
+    physics_timestep: float = 0.005
+    control_timestep: float = 0.1
+    max_control_steps_per_episode: int = 100
+    goal_distance_threshold: float = 0.02
+
+
+def build_robot_reach(config: RobotReachConfig | None = None) -> TaskBundle:
+    cfg = config or RobotReachConfig()
+    world = S.Body("world")
+    _arena_plane(world)
+    w3, acts = _ur5e(world)
+    _rigid_gripper(w3)
+    sc = S.Scene(world, actuators=acts, timestep=cfg.physics_timestep, integrator=1)
+    comp = compile_scene(sc)
+    t = MjsTask()
+    t.kind = MACROS["MJS_TASK_REACH"]
+    _robot_task_common(t, comp, cfg.control_timestep, cfg.physics_timestep, (0, 0, 0.174))
+    t.reward_type = 0 if cfg.reward_type == SPARSE_REWARD else 1
+    t.action_dim = 3
+    t.obs_dim = 6
+    t.goal_threshold = cfg.goal_distance_threshold
+    # the reference never terminates this task; episodes end through the composer time limit
+    t.time_limit = cfg.max_control_steps_per_episode * cfg.control_timestep
+    lo, hi = (-0.1, -0.6, 0.02), (0.1, -0.4, 0.2)  # robot_reach.py:108-110
+    t.set("spawn_lo", lo); t.set("spawn_hi", hi)
+    t.set("target_lo", lo); t.set("target_hi", hi)
+    t.set("action_lo", lo); t.set("action_hi", hi)
+    keys = [("ur5e/tcp_position", 3), ("target_position", 3)]
+    return TaskBundle("robot_reach", comp, t, keys, np.array(lo, np.float64), np.array(hi, np.float64), np.float64)
+
+
+def build_push_button(max_steps: int = 100) -> TaskBundle:
+    """RobotPushButtonTask scene (robot_push_button.py:56-119, props/switch.py:17-41),
+    state observations, ABS_JOINT_ACTION; rigid gripper."""
+    world = S.Body("world")
+    _arena_plane(world)
+    w3, acts = _ur5e(world)
+    _rigid_gripper(w3)
+    sw = world.add(S.Body("switch", pos=(0.0, -0.45, 0.0)))
+    sw.geoms.append(S.Geom(S.BOX, (0.025, 0.025, 0.025), pos=(0, 0, 0.025), name="switch/box"))
+    sw.geoms.append(S.Geom(S.CYLINDER, (0.02, 0.02), pos=(0, 0, 0.05), name="switch/button"))
+    sw.sites.append(S.Site("switch/button_site", pos=(0, 0, 0.05)))
+    sc = S.Scene(world, actuators=acts, timestep=0.005, integrator=1, ovr_body="switch",
+                 touch_site="switch/button_site", touch_size=(0.02 * 1.01, 0.02 * 1.01))
+    comp = compile_scene(sc)
+    t = MjsTask()
+    t.kind = MACROS["MJS_TASK_BUTTON"]
+    _robot_task_common(t, comp, 0.1, 0.005, (0, 0, 0.174))
+    t.reward_type = 0
+    t.action_dim = 7
+    t.obs_dim = 10
+    t.time_limit = max_steps * 0.1  # mujoco_sim/__init__.py:21,34
+    t.set("spawn_lo", (-0.2, -0.6, 0.02)); t.set("spawn_hi", (0.2, -0.3, 0.3))
+    t.set("target_lo", (-0.2, -0.6, 0.0)); t.set("target_hi", (0.2, -0.3, 0.1))
+    t.set("button_goal", (-0.3, -0.2, 0.3))
+    t.button_goal_radius = 0.05
+    t.touch_lo, t.touch_hi = 5.0, 200.0
+    # synthetic rollouts: q_now +- 0.05 rad handled on device (SURVEY.md 8d); box kept for the gripper dof
+    t.set("action_lo", [-0.05] * 6 + [0.0]); t.set("action_hi", [0.05] * 6 + [0.085])
+    keys = [("ur5e/joint_configuration", 6), ("unnamed_model/position", 3), ("unnamed_model/active", 1)]
+    return TaskBundle("robot_push_button", comp, t, keys, np.array([-3.14] * 6 + [0.0]), np.array([3.14] * 6 + [0.085]), np.float64)

@@ -36,3 +36,37 @@ def pointmass_states(n, seed, near_walls=True):
 def rel_err(a, b, floor=1e-3):
     a, b = np.asarray(a, float), np.asarray(b, float)
     return np.abs(a - b) / np.maximum(np.abs(b), floor)
+
+
+def push_states(bundle, n, seed, settle=True):
+    """Host-injected Planar Push states: IK'd arm pose, props dropped and settled by the oracle."""
+    import ctypes
+
+    from oracle.oracle import OracleEnvs, _dp, lib
+
+    rng = np.random.RandomState(seed)
+    t, m = bundle.task, bundle.model
+    ora = OracleEnvs(bundle, n)
+    for e in range(n):
+        s = ora.states[e]
+        while True:
+            tcp = np.array([rng.uniform(-0.2, 0.2), rng.uniform(-0.6, -0.3), 0.02])
+            objs = np.stack([rng.uniform(-0.15, 0.15, t.n_obj), rng.uniform(-0.55, -0.35, t.n_obj), rng.uniform(0.03, 0.08, t.n_obj)], 1)
+            d = [np.hypot(*(objs[i, :2] - objs[j, :2])) for i in range(t.n_obj) for j in range(i)]
+            d += [np.hypot(*(objs[i, :2] - tcp[:2])) for i in range(t.n_obj)]
+            if min(d) > 0.045:
+                break
+        q = np.zeros(6)
+        ok = lib().oracle_tcp_to_joints(ctypes.byref(t), _dp(tcp), _dp(np.zeros(6)), _dp(q))
+        assert ok
+        for i in range(6):
+            s.qpos[i] = q[i]
+            s.ctrl[i] = q[i]
+        for k in range(t.n_obj):
+            a = t.obj_qadr[k]
+            for i in range(3):
+                s.qpos[a + i] = objs[k, i]
+            s.qpos[a + 3] = 1.0
+        s.target[0], s.target[1], s.target[2] = rng.uniform(-0.15, 0.15), rng.uniform(-0.55, -0.35), 0.003
+    ora.finish_reset(150 if settle else 0)
+    return ora
