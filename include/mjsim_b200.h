@@ -67,6 +67,11 @@ int mjs_get_state(MjsSim* sim, MjsEnvState* h_states, int first, int count);
 int mjs_stats_device(MjsSim* sim, double** d_out);
 int mjs_stats(MjsSim* sim, double* h_out8, int reset);
 
+/* Planar Push prepares the next episode of finished envs (sampling + 150 settle
+ * steps) on an internal low-priority stream.  mjs_join_aux makes `stream` wait for
+ * whatever of that work is in flight (used to close a timed region). */
+int mjs_join_aux(MjsSim* sim, void* stream);
+
 /* Test hook: mj_forward for one env of an articulated task, dumping intermediate
  * stages (layout documented at arm_debug_kernel). */
 int mjs_debug_forward(MjsSim* sim, int env, double* h_out, int n);

@@ -319,6 +319,11 @@ int mjs_get_state(MjsSim* s, MjsEnvState* h, int first, int count) {
   return arm_get_state(s->arm, h, first, count);
 }
 
+int mjs_join_aux(MjsSim* s, void* stream) {
+  if (!s->arm) return 0;
+  return arm_join_aux(s->arm, (cudaStream_t)stream);
+}
+
 int mjs_debug_forward(MjsSim* s, int env, double* h_out, int n) {
   if (!s->arm) { mjs_set_error("mjs_debug_forward: articulated tasks only"); return -1; }
   MJS_CUDA_CHECK(cudaSetDevice(s->device));

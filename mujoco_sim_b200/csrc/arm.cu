@@ -1,10 +1,19 @@
 // arm.cu -- host side of the articulated (warp-per-env) engine.
+#include <cstdlib>
 #include <vector>
 
 #include "arm_api.cuh"
 #include "arm_kernel.cuh"
 
-#define ARM_WPB 4  // warps (= envs) per thread block
+#define ARM_WPB 4  // warps (= envs) per thread block (reset / forward / debug kernels)
+// Step kernel: one block of ARM_STEP_WPB warps per SM running the substep stages in
+// lock-step (barriers between stages) so the warps share their instruction fetches.
+#ifndef ARM_STEP_WPB
+#define ARM_STEP_WPB 16
+#endif
+#ifndef ARM_STEP_SYNC
+#define ARM_STEP_SYNC true
+#endif
 
 struct ArmSim {
   int N, nobj, precision;
@@ -17,32 +26,60 @@ struct ArmSim {
   ArmModel<float> mf;
   ArmModel<double> md;
   double* d_debug;
+  // pre-settled reset slots + side stream (tasks with settle steps)
+  double* slot_sd;
+  int* slot_si;
+  float* slot_obs;
+  int* slot_ready;
+  cudaStream_t side;
+  cudaEvent_t ev_step, ev_refill;
+  int refill_pending;
+  long long extra_launches;
 };
 
 template <int NOBJ>
 static void layout_sizes(int& sd, int& si) { sd = ArmLayout<NOBJ>::SD; si = ArmLayout<NOBJ>::SI; }
 
+// The kernels read the model from the __constant__ block c_arm_model.  It is
+// re-uploaded (after a device sync) whenever a different simulator or precision
+// launches on this device, so several simulators may coexist in a process.
+static const void* g_const_owner[64];
+template <typename real>
+static int bind_model(const ArmModel<real>& M) {
+  int dev = 0;
+  MJS_CUDA_CHECK(cudaGetDevice(&dev));
+  if (g_const_owner[dev & 63] == (const void*)&M) return 0;
+  MJS_CUDA_CHECK(cudaDeviceSynchronize());
+  MJS_CUDA_CHECK(cudaMemcpyToSymbol(c_arm_model, &M, sizeof(M)));
+  g_const_owner[dev & 63] = (const void*)&M;
+  return 0;
+}
+
 template <typename real, int NOBJ>
 static int launch(ArmSim* a, const ArmModel<real>& M, int which, ArmIO io, cudaStream_t st, int first = 0, int count = 0) {
+  if (bind_model<real>(M)) return -1;
   size_t smem = sizeof(WarpMem<real, NOBJ>) * ARM_WPB;
   int n = which == 2 ? count : a->N;
   int grid = (n + ARM_WPB - 1) / ARM_WPB;
   if (which == 0) {
-    auto k = arm_step_kernel<real, NOBJ, ARM_WPB>;
-    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<grid, ARM_WPB * 32, smem, st>>>(M, io);
+    // doubles need twice the shared memory: half the warps per block
+    constexpr int WPBS = sizeof(real) == 8 ? ARM_STEP_WPB / 2 : ARM_STEP_WPB;
+    auto k = arm_step_kernel<real, NOBJ, WPBS, ARM_STEP_SYNC>;
+    size_t smem_step = sizeof(WarpMem<real, NOBJ>) * WPBS;
+    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_step));
+    k<<<(n + WPBS - 1) / WPBS, WPBS * 32, smem_step, st>>>(io);
   } else if (which == 1) {
     auto k = arm_reset_kernel<real, NOBJ, ARM_WPB>;
     MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<grid, ARM_WPB * 32, smem, st>>>(M, io);
+    k<<<grid, ARM_WPB * 32, smem, st>>>(io, first);
   } else if (which == 3) {
     auto k = arm_debug_kernel<real, NOBJ, ARM_WPB>;
     MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<1, ARM_WPB * 32, smem, st>>>(M, io, first, a->d_debug);
+    k<<<1, ARM_WPB * 32, smem, st>>>(io, first, a->d_debug);
   } else {
     auto k = arm_forward_kernel<real, NOBJ, ARM_WPB>;
     MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<grid, ARM_WPB * 32, smem, st>>>(M, io, first, count);
+    k<<<grid, ARM_WPB * 32, smem, st>>>(io, first, count);
   }
   MJS_CUDA_CHECK(cudaGetLastError());
   return 1;
@@ -70,6 +107,20 @@ ArmSim* arm_create(const MjsModel& m, const MjsTask& t, int N, unsigned long lon
     mjs_set_error("arm engine: cudaMalloc failed"); delete a; return nullptr;
   }
   cudaMalloc(&a->d_debug, sizeof(double) * 1024);
+  if (a->mf.settle_steps > 0) {
+    if (cudaMalloc(&a->slot_sd, sizeof(double) * (size_t)a->SD * N) != cudaSuccess || cudaMalloc(&a->slot_si, sizeof(int) * (size_t)a->SI * N) != cudaSuccess ||
+        cudaMalloc(&a->slot_obs, sizeof(float) * 16 * (size_t)N) != cudaSuccess || cudaMalloc(&a->slot_ready, sizeof(int) * (size_t)N) != cudaSuccess) {
+      mjs_set_error("arm engine: cudaMalloc (reset slots) failed"); delete a; return nullptr;
+    }
+    cudaMemset(a->slot_sd, 0, sizeof(double) * (size_t)a->SD * N);
+    cudaMemset(a->slot_si, 0, sizeof(int) * (size_t)a->SI * N);
+    cudaMemset(a->slot_ready, 0, sizeof(int) * (size_t)N);
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    cudaStreamCreateWithPriority(&a->side, cudaStreamNonBlocking, lo);  // lowest priority: fills gaps
+    cudaEventCreateWithFlags(&a->ev_step, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&a->ev_refill, cudaEventDisableTiming);
+  }
   cudaMemset(a->sd, 0, sizeof(double) * (size_t)a->SD * N);
   cudaMemset(a->si, 0, sizeof(int) * (size_t)a->SI * N);
   return a;
@@ -77,21 +128,52 @@ ArmSim* arm_create(const MjsModel& m, const MjsTask& t, int N, unsigned long lon
 
 void arm_destroy(ArmSim* a) {
   if (!a) return;
-  cudaFree(a->sd); cudaFree(a->si);
+  for (int d = 0; d < 64; d++) if (g_const_owner[d] == (const void*)&a->mf || g_const_owner[d] == (const void*)&a->md) g_const_owner[d] = nullptr;
+  cudaFree(a->sd); cudaFree(a->si); cudaFree(a->d_debug);
+  if (a->slot_ready) {
+    cudaStreamSynchronize(a->side);
+    cudaFree(a->slot_sd); cudaFree(a->slot_si); cudaFree(a->slot_obs); cudaFree(a->slot_ready);
+    cudaStreamDestroy(a->side); cudaEventDestroy(a->ev_step); cudaEventDestroy(a->ev_refill);
+  }
   delete a;
 }
 
 static ArmIO make_io(ArmSim* a) {
   ArmIO io;
   memset(&io, 0, sizeof(io));
-  io.sd = a->sd; io.si = a->si; io.stats = a->d_stats; io.N = a->N; io.seed = a->seed; io.env_offset = a->env_offset;
+  { const char* lv = getenv("MJS_SYNC_LEVEL"); io.sync_level = lv ? atoi(lv) : 1; }
+  io.sd = a->sd; io.si = a->si; io.stats = a->d_stats;
+  io.slot_sd = a->slot_sd; io.slot_si = a->slot_si; io.slot_obs = a->slot_obs; io.slot_ready = a->slot_ready; io.N = a->N; io.seed = a->seed; io.env_offset = a->env_offset;
   return io;
+}
+
+// Launch the refill kernel on the low-priority side stream once the work already
+// queued on `st` is done, unless the previous refill is still running.
+static int maybe_refill(ArmSim* a, cudaStream_t st) {
+  if (!a->slot_ready) return 0;
+  if (a->refill_pending) {
+    cudaError_t q = cudaEventQuery(a->ev_refill);
+    if (q == cudaErrorNotReady) return 0;
+    if (q != cudaSuccess) { mjs_set_error("refill stream: %s", cudaGetErrorString(q)); return -1; }
+    a->refill_pending = 0;
+  }
+  MJS_CUDA_CHECK(cudaEventRecord(a->ev_step, st));
+  MJS_CUDA_CHECK(cudaStreamWaitEvent(a->side, a->ev_step, 0));
+  ArmIO io = make_io(a);
+  if (dispatch(a, 1, io, a->side, 1, 0) < 0) return -1;
+  MJS_CUDA_CHECK(cudaEventRecord(a->ev_refill, a->side));
+  a->refill_pending = 1;
+  a->extra_launches++;
+  return 1;
 }
 
 int arm_reset(ArmSim* a, const unsigned char* d_mask, float* d_obs, cudaStream_t st) {
   ArmIO io = make_io(a);
   io.mask = d_mask; io.obs = d_obs;
-  return dispatch(a, 1, io, st);
+  int r = dispatch(a, 1, io, st, 0, 0);
+  if (r < 0) return r;
+  int q = maybe_refill(a, st);
+  return q < 0 ? q : r + q;
 }
 
 int arm_step(ArmSim* a, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags, float* d_final_obs, int autoreset,
@@ -99,7 +181,17 @@ int arm_step(ArmSim* a, const float* d_actions, float* d_obs, float* d_reward, u
   ArmIO io = make_io(a);
   io.actions = d_actions; io.obs = d_obs; io.reward = d_reward; io.flags = d_flags; io.final_obs = d_final_obs;
   io.autoreset = autoreset; io.step_index = step_index;
-  return dispatch(a, 0, io, st);
+  if (!autoreset) { io.slot_ready = nullptr; }
+  int r = dispatch(a, 0, io, st);
+  if (r < 0) return r;
+  int q = autoreset ? maybe_refill(a, st) : 0;
+  return q < 0 ? q : r + q;
+}
+
+// make `st` wait for the refill work in flight (bench: close the timed region)
+int arm_join_aux(ArmSim* a, cudaStream_t st) {
+  if (a->slot_ready && a->refill_pending) MJS_CUDA_CHECK(cudaStreamWaitEvent(st, a->ev_refill, 0));
+  return 0;
 }
 
 template <int NOBJ>

@@ -11,3 +11,4 @@ int arm_step(ArmSim* a, const float* d_actions, float* d_obs, float* d_reward, u
 int arm_set_state(ArmSim* a, const MjsEnvState* h, int first, int count, int forward);
 int arm_get_state(ArmSim* a, MjsEnvState* h, int first, int count);
 int arm_debug_forward(ArmSim* a, int env, double* h_out, int n);
+int arm_join_aux(ArmSim* a, cudaStream_t st);

@@ -20,6 +20,13 @@
 
 #define FULLMASK 0xffffffffu
 
+// The specialised model lives in constant memory: every stage reads it as
+// constant-bank operands, and the heavy per-substep code can be one
+// non-inlined function (small instruction footprint) without passing it around.
+__constant__ __align__(16) unsigned char c_arm_model[sizeof(ArmModel<double>)];
+template <typename real>
+__device__ __forceinline__ const ArmModel<real>& cmodel() { return *reinterpret_cast<const ArmModel<real>*>(c_arm_model); }
+
 template <typename real, int NOBJ>
 struct WarpMem {
   static constexpr int NV = ARM_NLINK + 6 * NOBJ;
@@ -48,6 +55,9 @@ struct WarpMem {
   int blist[1 + ARM_MAXOBJ][ARM_MAXCB];  // contact | side<<8
   int ncon;
   int status;
+  int sync;     // lock-step mode: all warps of the block pass the stage barriers together
+  int coup;     // bit b: the arm block shares a contact with prop b
+  int objcoup;  // non-zero: two props share a contact (dense factorisation path)
 };
 
 // ------------------------------------------------------------------ warp helpers
@@ -69,7 +79,7 @@ template <typename real> __device__ __forceinline__ void sincos_r(real x, real* 
 template <> __device__ __forceinline__ void sincos_r<float>(float x, float* s, float* c) { sincosf(x, s, c); }
 template <> __device__ __forceinline__ void sincos_r<double>(double x, double* s, double* c) { sincos(x, s, c); }
 template <typename real> __device__ __forceinline__ real rsqrt_r(real x);
-template <> __device__ __forceinline__ float rsqrt_r<float>(float x) { return 1.0f / sqrtf(x); }
+template <> __device__ __forceinline__ float rsqrt_r<float>(float x) { return rsqrtf(x); }
 template <> __device__ __forceinline__ double rsqrt_r<double>(double x) { return 1.0 / sqrt(x); }
 
 template <typename real>
@@ -144,6 +154,12 @@ struct ArmEngine {
   __device__ static __forceinline__ int sidx(int dof) { return dof >= ARM_NLINK ? dof - ARM_NLINK : dof + 6 * NOBJ; }
   __device__ static __forceinline__ int dof_of_sidx(int s) { return s < 6 * NOBJ ? s + ARM_NLINK : s - 6 * NOBJ; }
   __device__ static __forceinline__ int blk_base(int blk) { return blk == 0 ? 0 : ARM_NLINK + 6 * (blk - 1); }
+
+  // Lock-step mode: the per-substep code is far larger than the instruction cache
+  // (L1.5 = 32 KB) and has almost no temporal reuse inside a warp, so warps that
+  // drift apart all stream their own instructions from L2.  Barriers between the
+  // stages keep the warps of a block inside the same code window.
+  __device__ static __forceinline__ void stage_sync(const WM& W, int level = 2) { if (W.sync >= level) __syncthreads(); }
 
   // ------------------------------------------------------------- [P1] kinematics
   // Restates mj_kinematics for the chain/free-body structure.  Leaves xpos/xmat of
@@ -576,7 +592,7 @@ struct ArmEngine {
         W.cpair[c] = code;
       }
     }
-    if (lane == 0) W.ncon = total;
+    if (lane == 0) { W.ncon = total; W.coup = 0; W.objcoup = 0; }
     if (lane <= ARM_MAXOBJ) W.bcount[lane] = 0;
     __syncwarp();
   }
@@ -693,6 +709,15 @@ struct ArmEngine {
       C.r0 = -bb * u[0] - kk * imp * (dist - incl);
 #pragma unroll
       for (int k = 0; k < 3; k++) C.rk[k] = -bb * C.mu[k] * u[1 + k];
+      // block coupling pattern of the Hessian
+      {
+        int ba = W.cblk[0][c], bb = W.cblk[1][c];
+        if (ba >= 0 && bb >= 0 && ba != bb) {
+          if (ba == 0) atomicOr(&W.coup, 1 << (bb - 1));
+          else if (bb == 0) atomicOr(&W.coup, 1 << (ba - 1));
+          else atomicOr(&W.objcoup, 1);
+        }
+      }
       // register this contact with the dof blocks it touches
 #pragma unroll
       for (int side = 0; side < 2; side++) {
@@ -773,6 +798,145 @@ struct ArmEngine {
     return s;
   }
 
+  // ---- Newton direction, block-sparse path.  Solver order: props first, arm last.
+  // Without prop-prop contacts the Hessian is block-arrow: the prop blocks are
+  // factorised in parallel (6 column steps for all props at once), then the arm
+  // rows against the coupled props, then the 6x6 arm Schur complement.
+  __device__ static __forceinline__ real block_direction(WM& W, int lane, real b) {
+    const bool isarm = lane < ARM_NLINK, isobj = lane >= ARM_NLINK && lane < NV;
+    const int myc = isarm ? lane : (lane - ARM_NLINK) % 6;
+    const int base = isarm ? 6 * NOBJ : ((lane - ARM_NLINK) / 6) * 6;
+    const int si = base + myc;
+    const int coup = W.coup;
+    real rdiag = 1;
+    // prop diagonal blocks
+#pragma unroll
+    for (int c = 0; c < 6; c++) {
+      real s = 0;
+      if (isobj && myc >= c) {
+        s = W.H[si][base + c];
+        for (int j = 0; j < c; j++) s -= W.H[si][base + j] * W.H[base + c][base + j];
+      }
+      real dk = shfl(s, isobj ? ARM_NLINK + base + c : lane);
+      real rd = rsqrt_r<real>(dk);
+      if (isobj) {
+        if (myc == c) { W.H[si][si] = dk * rd; rdiag = rd; }
+        else if (myc > c) W.H[si][base + c] = s * rd;
+      }
+      __syncwarp();
+    }
+    // arm rows x coupled prop columns
+    for (int ob = 0; ob < NOBJ; ob++) {
+      if (!((coup >> ob) & 1)) continue;
+#pragma unroll
+      for (int c = 0; c < 6; c++) {
+        int k = 6 * ob + c;
+        real rdk = shfl(rdiag, ARM_NLINK + k);
+        if (isarm) {
+          real s = W.H[si][k];
+          for (int j = 0; j < c; j++) s -= W.H[si][6 * ob + j] * W.H[k][6 * ob + j];
+          W.H[si][k] = s * rdk;
+        }
+      }
+    }
+    __syncwarp();
+    // arm Schur complement block
+#pragma unroll
+    for (int c = 0; c < 6; c++) {
+      int k = 6 * NOBJ + c;
+      real s = 0;
+      if (isarm && myc >= c) {
+        s = W.H[si][k];
+        for (int ob = 0; ob < NOBJ; ob++) {
+          if (!((coup >> ob) & 1)) continue;
+#pragma unroll
+          for (int j = 0; j < 6; j++) s -= W.H[si][6 * ob + j] * W.H[k][6 * ob + j];
+        }
+        for (int j = 0; j < c; j++) s -= W.H[si][6 * NOBJ + j] * W.H[k][6 * NOBJ + j];
+      }
+      real dk = shfl(s, c);
+      real rd = rsqrt_r<real>(dk);
+      if (isarm) {
+        if (myc == c) { W.H[si][si] = dk * rd; rdiag = rd; }
+        else if (myc > c) W.H[si][k] = s * rd;
+      }
+      __syncwarp();
+    }
+    // forward substitution: props in parallel, then arm
+#pragma unroll
+    for (int c = 0; c < 6; c++) {
+      real yk = shfl(b * rdiag, isobj ? ARM_NLINK + base + c : lane);
+      if (isobj) { if (myc == c) b = yk; else if (myc > c) b -= W.H[si][base + c] * yk; }
+    }
+    if (isobj) W.dir[lane] = b;
+    __syncwarp();
+    if (isarm) {
+      for (int ob = 0; ob < NOBJ; ob++) {
+        if (!((coup >> ob) & 1)) continue;
+#pragma unroll
+        for (int j = 0; j < 6; j++) b -= W.H[si][6 * ob + j] * W.dir[ARM_NLINK + 6 * ob + j];
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 6; c++) {
+      real yk = shfl(b * rdiag, c);
+      if (isarm) { if (myc == c) b = yk; else if (myc > c) b -= W.H[si][6 * NOBJ + c] * yk; }
+    }
+    // backward substitution: arm, then props
+#pragma unroll
+    for (int c = 5; c >= 0; c--) {
+      real xk = shfl(b * rdiag, c);
+      if (isarm) { if (myc == c) b = xk; else if (myc < c) b -= W.H[6 * NOBJ + c][si] * xk; }
+    }
+    __syncwarp();
+    if (isarm) W.dir[lane] = b;
+    __syncwarp();
+    if (isobj && ((coup >> (base / 6)) & 1)) {
+#pragma unroll
+      for (int i = 0; i < 6; i++) b -= W.H[6 * NOBJ + i][si] * W.dir[i];
+    }
+#pragma unroll
+    for (int c = 5; c >= 0; c--) {
+      real xk = shfl(b * rdiag, isobj ? ARM_NLINK + base + c : lane);
+      if (isobj) { if (myc == c) b = xk; else if (myc < c) b -= W.H[base + c][si] * xk; }
+    }
+    return (isarm || isobj) ? b : (real)0;
+  }
+
+  // ---- Newton direction, dense path (prop-prop contacts present): lane = row,
+  // left-looking column Cholesky over the whole NV x NV Hessian.
+  __device__ static __noinline__ real dense_direction(WM& W, int lane, real b) {
+    const bool isdof = lane < NV;
+    const int si = isdof ? sidx(lane) : 0;
+    real rdiag = 1;
+    for (int k = 0; k < NV; k++) {
+      real s = 0;
+      if (isdof && si >= k) {
+        s = W.H[si][k];
+        for (int j = 0; j < k; j++) s -= W.H[si][j] * W.H[k][j];
+      }
+      int owner = dof_of_sidx(k);
+      real dk = shfl(s, owner);
+      real rd = rsqrt_r<real>(dk);
+      if (isdof) {
+        if (si == k) { W.H[si][k] = dk * rd; rdiag = rd; }
+        else if (si > k) W.H[si][k] = s * rd;
+      }
+      __syncwarp();
+    }
+    for (int k = 0; k < NV; k++) {
+      int owner = dof_of_sidx(k);
+      real yk = shfl(b * rdiag, owner);
+      if (isdof) { if (si == k) b = yk; else if (si > k) b -= W.H[si][k] * yk; }
+    }
+    for (int k = NV - 1; k >= 0; k--) {
+      int owner = dof_of_sidx(k);
+      real xk = shfl(b * rdiag, owner);
+      if (isdof) { if (si == k) b = xk; else if (si < k) b -= W.H[k][si] * xk; }
+    }
+    return isdof ? b : (real)0;
+  }
+
   // Primal Newton with a safeguarded-Newton exact line search (cost is piecewise
   // quadratic).  On exit W.a = qacc, W.fcon = qfrc_constraint.  Returns iterations.
   __device__ static int solve(const AM& A, WM& W, int lane, ConReg& C, real& a_i) {
@@ -796,148 +960,138 @@ struct ArmEngine {
     real prev_cost = 0;
     int it = 0;
     const real fsm_i = isdof ? W.fsm[lane] : (real)0;
+    bool done = false;
+    int nit = 0;
     for (; it < A.max_iter; it++) {
-      real ccost = contact_eval(W, lane, C, true);
-      __syncwarp();
-      // gradient and cost
-      real Ma = 0, grad = 0;
-      if (isdof) {
-        if (lane < ARM_NLINK) {
-#pragma unroll
-          for (int j = 0; j < ARM_NLINK; j++) Ma += W.Marm[lane][j] * W.a[j];
-        } else Ma = mdiag * a_i;
-        grad = Ma - fsm_i - jt_force(W, myblk, d);
+      real Ma = 0, grad = 0, ccost = 0, cost = 0, gn = 0, dir_i = 0;
+      if (!done) {
+        ccost = contact_eval(W, lane, C, true);
+        __syncwarp();
+        // gradient and cost
+        if (isdof) {
+          if (lane < ARM_NLINK) {
+  #pragma unroll
+            for (int j = 0; j < ARM_NLINK; j++) Ma += W.Marm[lane][j] * W.a[j];
+          } else Ma = mdiag * a_i;
+          grad = Ma - fsm_i - jt_force(W, myblk, d);
+        }
+        cost = warp_sum(ccost + (isdof ? a_i * ((real)0.5 * Ma - fsm_i) : (real)0));
+        gn = sqrt(warp_sum(grad * grad));
+        if (it > 0 && (prev_cost - cost) * A.scale < A.tol) done = true;
+        if (gn * A.scale < A.tol) done = true;
+        prev_cost = cost;
       }
-      real cost = warp_sum(ccost + (isdof ? a_i * ((real)0.5 * Ma - fsm_i) : (real)0));
-      real gn = sqrt(warp_sum(grad * grad));
-      if (it > 0 && (prev_cost - cost) * A.scale < A.tol) break;
-      if (gn * A.scale < A.tol) break;
-      prev_cost = cost;
-      // ---- Hessian rows H = M + sum_c Jc^T W_c Jc (solver ordering)
-      if (isdof) {
-        for (int j = 0; j < NV; j++) W.H[si][j] = 0;
-        if (lane < ARM_NLINK) {
-#pragma unroll
-          for (int j = 0; j < ARM_NLINK; j++) W.H[si][sidx(j)] = W.Marm[lane][j];
-        } else W.H[si][si] = mdiag;
-        int n = W.bcount[myblk];
-        for (int r = 0; r < n; r++) {
-          int e = W.blist[myblk][r], c = e & 0xff, side = e >> 8;
-          real jm[4], z[4];
-#pragma unroll
-          for (int k = 0; k < 4; k++) jm[k] = W.cJ[(side * 4 + k) * 6 + d][c];
-          z[0] = W.cW[0][c] * jm[0] + W.cW[1][c] * jm[1] + W.cW[2][c] * jm[2] + W.cW[3][c] * jm[3];
-#pragma unroll
-          for (int k = 0; k < 3; k++) z[1 + k] = W.cW[1 + k][c] * jm[0] + W.cW[4 + k][c] * jm[1 + k];
-#pragma unroll
-          for (int s2 = 0; s2 < 2; s2++) {
-            int blk2 = W.cblk[s2][c];
-            if (blk2 < 0) continue;
-            int b2 = blk_base(blk2), cols2 = W.ccols[s2][c];
-            for (int j = 0; j < cols2; j++) {
-              real t = 0;
-#pragma unroll
-              for (int k = 0; k < 4; k++) t += z[k] * W.cJ[(s2 * 4 + k) * 6 + j][c];
-              W.H[si][sidx(b2 + j)] += t;
+      // lock-step mode: the block leaves the loop together (shared instruction fetch)
+      if (W.sync) { if (!__syncthreads_or(!done)) break; }
+      else if (done) break;
+      if (!done) {
+        nit++;
+        // ---- Hessian rows H = M + sum_c Jc^T W_c Jc (solver ordering)
+        if (isdof) {
+          for (int j = 0; j < NV; j++) W.H[si][j] = 0;
+          if (lane < ARM_NLINK) {
+  #pragma unroll
+            for (int j = 0; j < ARM_NLINK; j++) W.H[si][sidx(j)] = W.Marm[lane][j];
+          } else W.H[si][si] = mdiag;
+          int n = W.bcount[myblk];
+          for (int r = 0; r < n; r++) {
+            int e = W.blist[myblk][r], c = e & 0xff, side = e >> 8;
+            real jm[4], z[4];
+  #pragma unroll
+            for (int k = 0; k < 4; k++) jm[k] = W.cJ[(side * 4 + k) * 6 + d][c];
+            z[0] = W.cW[0][c] * jm[0] + W.cW[1][c] * jm[1] + W.cW[2][c] * jm[2] + W.cW[3][c] * jm[3];
+  #pragma unroll
+            for (int k = 0; k < 3; k++) z[1 + k] = W.cW[1 + k][c] * jm[0] + W.cW[4 + k][c] * jm[1 + k];
+  #pragma unroll
+            for (int s2 = 0; s2 < 2; s2++) {
+              int blk2 = W.cblk[s2][c];
+              if (blk2 < 0) continue;
+              int b2 = blk_base(blk2), cols2 = W.ccols[s2][c];
+              for (int j = 0; j < cols2; j++) {
+                real t = 0;
+  #pragma unroll
+                for (int k = 0; k < 4; k++) t += z[k] * W.cJ[(s2 * 4 + k) * 6 + j][c];
+                W.H[si][sidx(b2 + j)] += t;
+              }
             }
           }
-        }
-      }
-      __syncwarp();
-      // ---- Cholesky H = L L^T, lane = row, left-looking by column
-      real rdiag = 1;
-      for (int k = 0; k < NV; k++) {
-        real s = 0;
-        if (isdof && si >= k) {
-          s = W.H[si][k];
-          for (int j = 0; j < k; j++) s -= W.H[si][j] * W.H[k][j];
-        }
-        int owner = dof_of_sidx(k);
-        real dk = shfl(s, owner);
-        real rd = rsqrt_r<real>(dk);
-        if (isdof) {
-          if (si == k) { W.H[si][k] = dk * rd; rdiag = rd; }
-          else if (si > k) W.H[si][k] = s * rd;
         }
         __syncwarp();
       }
-      // ---- solve L L^T dir = -grad
-      real b = -grad;
-      for (int k = 0; k < NV; k++) {
-        int owner = dof_of_sidx(k);
-        real yk = shfl(b * rdiag, owner);
-        if (isdof) { if (si == k) b = yk; else if (si > k) b -= W.H[si][k] * yk; }
+      stage_sync(W);
+      if (!done) {
+        real b = -grad;
+        if (W.objcoup == 0) b = block_direction(W, lane, b);
+        else b = dense_direction(W, lane, b);
+        dir_i = isdof ? b : (real)0;
+        if (isdof) W.dir[lane] = dir_i;
+        __syncwarp();
       }
-      for (int k = NV - 1; k >= 0; k--) {
-        int owner = dof_of_sidx(k);
-        real xk = shfl(b * rdiag, owner);
-        if (isdof) { if (si == k) b = xk; else if (si < k) b -= W.H[k][si] * xk; }
-      }
-      real dir_i = isdof ? b : (real)0;
-      if (isdof) W.dir[lane] = dir_i;
-      __syncwarp();
-      // ---- exact line search along dir
-      real Md = 0;
-      if (isdof) {
-        if (lane < ARM_NLINK) {
-#pragma unroll
-          for (int j = 0; j < ARM_NLINK; j++) Md += W.Marm[lane][j] * W.dir[j];
-        } else Md = mdiag * dir_i;
-      }
-      real q1 = warp_sum(isdof ? dir_i * (Ma - fsm_i) : (real)0);
-      real q2 = warp_sum(isdof ? dir_i * Md : (real)0);
-      {
-        real u[4];
-        contact_apply(W, lane, C, W.dir, u);
-        C.de0 = u[0];
-#pragma unroll
-        for (int k = 0; k < 3; k++) C.dek[k] = C.mu[k] * u[1 + k];
-      }
-      real alpha = 0, lo = 0, hi = (real)-1, s_lo = 0;
-      real s0abs = 0;
-      const int LSMAX = sizeof(real) == 8 ? 40 : 12;
-      for (int ls = 0; ls < LSMAX; ls++) {
-        // derivative and curvature of the cost at alpha
-        real sl = 0, cu = 0;
-        if (C.dim == 1) {
-          real jar = C.e0 + alpha * C.de0;
-          if (jar < 0 || (jar == 0 && C.de0 < 0)) { sl = C.D * jar * C.de0; cu = C.D * C.de0 * C.de0; }
-        } else if (C.dim > 1) {
-#pragma unroll
-          for (int k = 0; k < 3; k++) {
-            if (k < C.dim - 1) {
-              real jp = C.e0 + C.ek[k] + alpha * (C.de0 + C.dek[k]), dp = C.de0 + C.dek[k];
-              real jm = C.e0 - C.ek[k] + alpha * (C.de0 - C.dek[k]), dm = C.de0 - C.dek[k];
-              if (jp < 0 || (jp == 0 && dp < 0)) { sl += C.D * jp * dp; cu += C.D * dp * dp; }
-              if (jm < 0 || (jm == 0 && dm < 0)) { sl += C.D * jm * dm; cu += C.D * dm * dm; }
+      stage_sync(W);
+      if (!done) {
+        // ---- exact line search along dir
+        real Md = 0;
+        if (isdof) {
+          if (lane < ARM_NLINK) {
+  #pragma unroll
+            for (int j = 0; j < ARM_NLINK; j++) Md += W.Marm[lane][j] * W.dir[j];
+          } else Md = mdiag * dir_i;
+        }
+        real q1 = warp_sum(isdof ? dir_i * (Ma - fsm_i) : (real)0);
+        real q2 = warp_sum(isdof ? dir_i * Md : (real)0);
+        {
+          real u[4];
+          contact_apply(W, lane, C, W.dir, u);
+          C.de0 = u[0];
+  #pragma unroll
+          for (int k = 0; k < 3; k++) C.dek[k] = C.mu[k] * u[1 + k];
+        }
+        real alpha = 0, lo = 0, hi = (real)-1, s_lo = 0;
+        real s0abs = 0;
+        const int LSMAX = sizeof(real) == 8 ? 40 : 12;
+        for (int ls = 0; ls < LSMAX; ls++) {
+          // derivative and curvature of the cost at alpha
+          real sl = 0, cu = 0;
+          if (C.dim == 1) {
+            real jar = C.e0 + alpha * C.de0;
+            if (jar < 0 || (jar == 0 && C.de0 < 0)) { sl = C.D * jar * C.de0; cu = C.D * C.de0 * C.de0; }
+          } else if (C.dim > 1) {
+  #pragma unroll
+            for (int k = 0; k < 3; k++) {
+              if (k < C.dim - 1) {
+                real jp = C.e0 + C.ek[k] + alpha * (C.de0 + C.dek[k]), dp = C.de0 + C.dek[k];
+                real jm = C.e0 - C.ek[k] + alpha * (C.de0 - C.dek[k]), dm = C.de0 - C.dek[k];
+                if (jp < 0 || (jp == 0 && dp < 0)) { sl += C.D * jp * dp; cu += C.D * dp * dp; }
+                if (jm < 0 || (jm == 0 && dm < 0)) { sl += C.D * jm * dm; cu += C.D * dm * dm; }
+              }
             }
           }
+          sl = warp_sum(sl) + q1 + alpha * q2;
+          cu = warp_sum(cu) + q2;
+          if (ls == 0) s0abs = fabs(sl);
+          const real lstol = sizeof(real) == 8 ? (real)1e-14 : (real)1e-6;
+          if (fabs(sl) <= lstol * s0abs || cu <= 0) break;
+          if (sl < 0) { lo = alpha; s_lo = sl; } else hi = alpha;
+          real an = alpha - sl / cu;
+          if (hi >= 0 && !(an > lo && an < hi)) an = (real)0.5 * (lo + hi);
+          if (an == alpha) break;
+          alpha = an;
         }
-        sl = warp_sum(sl) + q1 + alpha * q2;
-        cu = warp_sum(cu) + q2;
-        if (ls == 0) s0abs = fabs(sl);
-        const real lstol = sizeof(real) == 8 ? (real)1e-14 : (real)1e-6;
-        if (fabs(sl) <= lstol * s0abs || cu <= 0) break;
-        if (sl < 0) { lo = alpha; s_lo = sl; } else hi = alpha;
-        real an = alpha - sl / cu;
-        if (hi >= 0 && !(an > lo && an < hi)) an = (real)0.5 * (lo + hi);
-        if (an == alpha) break;
-        alpha = an;
+        (void)s_lo;
+        a_i += alpha * dir_i;
+        if (isdof) W.a[lane] = a_i;
+        C.e0 += alpha * C.de0;
+  #pragma unroll
+        for (int k = 0; k < 3; k++) C.ek[k] += alpha * C.dek[k];
+        __syncwarp();
       }
-      (void)s_lo;
-      a_i += alpha * dir_i;
-      if (isdof) W.a[lane] = a_i;
-      C.e0 += alpha * C.de0;
-#pragma unroll
-      for (int k = 0; k < 3; k++) C.ek[k] += alpha * C.dek[k];
-      __syncwarp();
     }
     // final forces -> qfrc_constraint
     contact_eval(W, lane, C, true);
     __syncwarp();
     if (isdof) W.fcon[lane] = jt_force(W, myblk, d);
     __syncwarp();
-    return it;
+    return nit;
   }
 
   // ----------------------------------------------------- [P10] touch sensor (mj_sensorAcc)
@@ -1035,24 +1189,36 @@ struct ArmEngine {
   }
 
   // ------------------------------------------------ one physics substep (legacy_step)
-  struct SubOut { real touch; int niter; };
+  struct SubRes { real a_i; double time; real touch; int niter; };
 
-  // mj_step1 for the current (qpos, qvel): everything up to the constraint rows
-  __device__ static bool step1(const AM& A, WM& W, int lane, ConReg& C) {
+  // One physics step for the current (qpos, qvel, ctrl): mj_step1 (kinematics ..
+  // constraint rows) followed by mj_step2 (solve, touch sensor, integrate).  The
+  // composer loop's "step2 then step1" order is the same sequence seen from the
+  // state's point of view (ArmTask::control_step).  Deliberately NOT inlined:
+  // one copy of the heavy code keeps the instruction footprint inside the i-cache.
+  __device__ static __noinline__ SubRes substep(WM* Wp, int lane, real a_i, double time, int do_integrate) {
+    const AM& A = cmodel<real>();
+    WM& W = *Wp;
+    ConReg C;
+    stage_sync(W, 1);
     kinematics(A, W, lane);
+    stage_sync(W);
     bool clamped = dynamics(A, W, lane);
+    stage_sync(W);
     collide(A, W, lane);
+    stage_sync(W);
     make_rows(A, W, lane, C);
-    return clamped;
-  }
-  // mj_step2: solve, sensor, integrate.  a_i = warm start in, qacc out.
-  __device__ static SubOut step2(const AM& A, WM& W, int lane, ConReg& C, bool clamped, real& a_i, double& time, bool do_integrate) {
-    SubOut o;
-    o.niter = solve(A, W, lane, C, a_i);
-    o.touch = touch_force(A, W, lane, C);
+    stage_sync(W, 1);
+    SubRes r;
+    r.niter = solve(A, W, lane, C, a_i);
+    r.touch = touch_force(A, W, lane, C);
+    stage_sync(W);
     if (do_integrate) integrate(A, W, lane, clamped, time);
-    return o;
+    r.a_i = a_i;
+    r.time = time;
+    return r;
   }
+  __device__ static __noinline__ void kinematics_only(WM* Wp, int lane) { kinematics(cmodel<real>(), *Wp, lane); }
 };
 
 // ===================================================================== analytic UR IK
@@ -1179,6 +1345,12 @@ struct ArmIO {
   int N, autoreset;
   unsigned long long seed;
   unsigned int env_offset, step_index;
+  int sync_level;
+  // pre-settled next-episode states (tasks with settle steps): see arm_reset_kernel
+  double* slot_sd;
+  int* slot_si;
+  float* slot_obs;
+  int* slot_ready;
 };
 
 template <typename real, int NOBJ>
@@ -1201,7 +1373,7 @@ struct ArmTask {
     return lo + (hi - lo) * u;
   }
 
-  __device__ static void load(const AM& A, WM& W, const ArmIO& io, int e, int lane, TS& T, real& a_i) {
+  __device__ static void load(const AM& A, WM& W, const ArmIO& io, int e, int lane, TS& T, real& a_i, int sync = 0) {
     const double* s = io.sd + (size_t)e * L::SD;
     for (int k = lane; k < NQ; k += 32) W.qpos[k] = s[L::QPOS + k];
     if (lane < NV) { W.qvel[lane] = s[L::QVEL + lane]; a_i = (real)s[L::WARM + lane]; } else a_i = 0;
@@ -1211,7 +1383,7 @@ struct ArmTask {
     const int* si = io.si + (size_t)e * L::SI;
     T.step = si[L::I_STEP]; T.traj = si[L::I_TRAJ]; T.swa = si[L::I_SWA]; T.swp = si[L::I_SWP]; T.swc = si[L::I_SWC];
     T.status = si[L::I_STATUS]; T.episode = si[L::I_EPISODE]; T.len = si[L::I_LEN];
-    if (lane == 0) W.status = 0;
+    if (lane == 0) { W.status = 0; W.sync = sync; }
     init_static(A, W, lane, T);
     __syncwarp();
   }
@@ -1334,7 +1506,6 @@ struct ArmTask {
 
   // One control step for the env owned by this warp (composer loop)
   __device__ static void control_step(const AM& A, WM& W, int lane, TS& T, real& a_i, const double* action, Out& o) {
-    typename E::ConReg C;
     if (A.kind == MJS_TASK_REACH) servoL(A, W, lane, T, action);
     else if (A.kind == MJS_TASK_PUSH) {
       T.step += 1;
@@ -1346,11 +1517,11 @@ struct ArmTask {
     }
     for (int k = 0; k < A.n_sub; k++) {
       before_substep(A, W, lane, T);
-      bool clamped = E::step1(A, W, lane, C);
-      typename E::SubOut so = E::step2(A, W, lane, C, clamped, a_i, T.time, true);
+      typename E::SubRes so = E::substep(&W, lane, a_i, T.time, 1);
+      a_i = so.a_i; T.time = so.time;
       if (A.kind == MJS_TASK_BUTTON) switch_update(A, T, so.touch);
     }
-    E::kinematics(A, W, lane);
+    E::kinematics_only(&W, lane);
     observe(A, W, T, o);
     T.ret += o.reward;
     T.len += 1;
@@ -1402,16 +1573,22 @@ struct ArmTask {
     a_i = 0;
     init_static(A, W, lane, T);
     __syncwarp();
-    // mj_forward at the reset state (actuator force is zero: ctrl == qpos, qvel == 0)
-    typename E::ConReg C;
-    bool clamped = E::step1(A, W, lane, C);
-    typename E::SubOut so = E::step2(A, W, lane, C, clamped, a_i, T.time, false);
-    for (int k = 0; k < A.settle_steps; k++) {
-      E::step2(A, W, lane, C, clamped, a_i, T.time, true);  // re-solve + integrate (mj_step2)
-      clamped = E::step1(A, W, lane, C);                      // mj_step1
+    // mj_forward at the reset state (actuator force is zero: ctrl == qpos, qvel == 0),
+    // then the settle steps (robot_planar_push.py:160-161).  substep = step1 + step2, so
+    // N settle steps are N substeps; the reference's extra re-solve of the forward pass
+    // restarts from a converged warm start and changes nothing.
+    typename E::SubRes so;
+    if (A.settle_steps > 0) {
+      for (int k = 0; k < A.settle_steps; k++) {
+        so = E::substep(&W, lane, a_i, T.time, 1);
+        a_i = so.a_i; T.time = so.time;
+      }
       so.touch = 0;
+      E::kinematics_only(&W, lane);
+    } else {
+      so = E::substep(&W, lane, a_i, T.time, 0);
+      a_i = so.a_i;
     }
-    if (A.settle_steps > 0) { E::kinematics(A, W, lane); }
     if (A.kind == MJS_TASK_BUTTON) switch_update(A, T, so.touch);
     observe(A, W, T, o);
   }
@@ -1434,19 +1611,24 @@ __device__ __forceinline__ void arm_write_out(const ArmModel<real>& A, const Arm
   }
 }
 
-template <typename real, int NOBJ, int WPB>
-__global__ void __launch_bounds__(WPB * 32) arm_step_kernel(const __grid_constant__ ArmModel<real> A, ArmIO io) {
+template <typename real, int NOBJ, int WPB, bool SYNC>
+__global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
+  const ArmModel<real>& A = cmodel<real>();
   using TK = ArmTask<real, NOBJ>;
   using WM = WarpMem<real, NOBJ>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   WM* wm = reinterpret_cast<WM*>(smem_raw);
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int e = blockIdx.x * WPB + warp;
-  if (e >= io.N) return;
+  bool valid = e < io.N;
+  if (!valid) {
+    if (!SYNC) return;
+    e = io.N - 1;  // lock-step mode: surplus warps shadow the last env (barrier counts must match), write nothing
+  }
   WM& W = wm[warp];
   typename TK::TS T;
   real a_i;
-  TK::load(A, W, io, e, lane, T, a_i);
+  TK::load(A, W, io, e, lane, T, a_i, SYNC ? io.sync_level : 0);
   // action (all lanes hold the full vector)
   double action[8];
   int AD = A.action_dim;
@@ -1466,6 +1648,10 @@ __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(const __grid_constan
   }
   typename TK::Out o;
   TK::control_step(A, W, lane, T, a_i, action, o);
+  if (!valid) return;  // all barriers of this launch are behind us
+  __syncwarp();
+  if (lane == 0) W.sync = 0;  // an inline reset below runs on its own: no further block barriers
+  __syncwarp();
   if (io.final_obs && lane < A.obs_dim) {
     double v = 0;
 #pragma unroll
@@ -1482,6 +1668,30 @@ __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(const __grid_constan
     }
   }
   if (o.done && io.autoreset) {
+    using L = ArmLayout<NOBJ>;
+    // Fast path: adopt the pre-settled next episode prepared by the refill kernel on
+    // the side stream (Planar Push resets cost 150 physics steps; doing them inline
+    // would stretch this launch 8x for the whole GPU).
+    bool took = false;
+    if (io.slot_ready) {
+      int rdy = 0;
+      if (lane == 0) {
+        rdy = *((volatile int*)(io.slot_ready + e));
+        if (rdy) { __threadfence(); rdy = (io.slot_si[(size_t)e * L::SI + L::I_EPISODE] == T.episode + 1) ? 1 : 0; }
+      }
+      rdy = __shfl_sync(FULLMASK, rdy, 0);
+      if (rdy) {
+        const double* src = io.slot_sd + (size_t)e * L::SD;
+        double* dst = io.sd + (size_t)e * L::SD;
+        for (int k = lane; k < L::SD; k += 32) dst[k] = src[k];
+        if (lane < L::SI) io.si[(size_t)e * L::SI + lane] = io.slot_si[(size_t)e * L::SI + lane];
+        if (io.obs && lane < A.obs_dim) io.obs[(size_t)e * A.obs_dim + lane] = io.slot_obs[(size_t)e * 16 + lane];
+        __syncwarp();
+        if (lane == 0) { __threadfence(); *((volatile int*)(io.slot_ready + e)) = 0; }
+        took = true;
+      }
+    }
+    if (took) return;
     typename TK::Out o2;
     T.status |= W.status;
     TK::reset_env(A, W, lane, io, e, T, a_i, o2);
@@ -1492,8 +1702,12 @@ __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(const __grid_constan
   TK::store(W, io, e, lane, T, a_i);
 }
 
+// refill == 0: reset the masked envs in place (mjs_reset).
+// refill == 1: for every env whose slot is empty, generate its NEXT episode (sampling,
+//              IK, mj_forward, settle steps) into the slot arrays and mark it ready.
 template <typename real, int NOBJ, int WPB>
-__global__ void __launch_bounds__(WPB * 32) arm_reset_kernel(const __grid_constant__ ArmModel<real> A, ArmIO io) {
+__global__ void __launch_bounds__(WPB * 32) arm_reset_kernel(ArmIO io, int refill) {
+  const ArmModel<real>& A = cmodel<real>();
   using TK = ArmTask<real, NOBJ>;
   using WM = WarpMem<real, NOBJ>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1501,20 +1715,39 @@ __global__ void __launch_bounds__(WPB * 32) arm_reset_kernel(const __grid_consta
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int e = blockIdx.x * WPB + warp;
   if (e >= io.N) return;
-  if (io.mask && !io.mask[e]) return;
+  if (refill) {
+    if (*((volatile int*)(io.slot_ready + e)) != 0) return;
+  } else if (io.mask && !io.mask[e]) return;
   WM& W = wm[warp];
   typename TK::TS T;
   real a_i;
   TK::load(A, W, io, e, lane, T, a_i);
   typename TK::Out o;
   TK::reset_env(A, W, lane, io, e, T, a_i, o);
-  arm_write_out<real, NOBJ>(A, io, e, lane, o, false);
-  TK::store(W, io, e, lane, T, a_i);
+  if (refill) {
+    ArmIO io2 = io;
+    io2.sd = io.slot_sd; io2.si = io.slot_si;
+    T.status = 0;
+    TK::store(W, io2, e, lane, T, a_i);
+    if (lane < 16) {
+      double v = 0;
+#pragma unroll
+      for (int k = 0; k < 16; k++) if (k == lane) v = o.obs[k];
+      io.slot_obs[(size_t)e * 16 + lane] = (float)v;
+    }
+    __syncwarp();
+    if (lane == 0) { __threadfence(); *((volatile int*)(io.slot_ready + e)) = 1; }
+  } else {
+    arm_write_out<real, NOBJ>(A, io, e, lane, o, false);
+    TK::store(W, io, e, lane, T, a_i);
+    if (io.slot_ready && lane == 0) *((volatile int*)(io.slot_ready + e)) = 0;  // a stale slot would repeat this episode
+  }
 }
 
 // mj_forward on injected states (mjs_set_state with forward != 0): refresh the warm start
 template <typename real, int NOBJ, int WPB>
-__global__ void __launch_bounds__(WPB * 32) arm_forward_kernel(const __grid_constant__ ArmModel<real> A, ArmIO io, int first, int count) {
+__global__ void __launch_bounds__(WPB * 32) arm_forward_kernel(ArmIO io, int first, int count) {
+  const ArmModel<real>& A = cmodel<real>();
   using TK = ArmTask<real, NOBJ>;
   using E = ArmEngine<real, NOBJ>;
   using WM = WarpMem<real, NOBJ>;
@@ -1527,16 +1760,16 @@ __global__ void __launch_bounds__(WPB * 32) arm_forward_kernel(const __grid_cons
   typename TK::TS T;
   real a_i;
   TK::load(A, W, io, e, lane, T, a_i);
-  typename E::ConReg C;
-  bool clamped = E::step1(A, W, lane, C);
-  E::step2(A, W, lane, C, clamped, a_i, T.time, false);
+  typename E::SubRes so = E::substep(&W, lane, a_i, T.time, 0);
+  a_i = so.a_i;
   TK::store(W, io, e, lane, T, a_i);
 }
 
 // debug: run mj_forward for one env and dump intermediate stages (tests only)
 //   out: [0..35] Marm, [36..36+NV) fsm, [..+NV) qacc, [..+NV) fcon, then ncon, then per contact (dist,pos3,normal3) x ncon, then link xpos (18), S (36)
 template <typename real, int NOBJ, int WPB>
-__global__ void __launch_bounds__(WPB * 32) arm_debug_kernel(const __grid_constant__ ArmModel<real> A, ArmIO io, int env, double* out) {
+__global__ void __launch_bounds__(WPB * 32) arm_debug_kernel(ArmIO io, int env, double* out) {
+  const ArmModel<real>& A = cmodel<real>();
   using TK = ArmTask<real, NOBJ>;
   using E = ArmEngine<real, NOBJ>;
   using WM = WarpMem<real, NOBJ>;
@@ -1548,9 +1781,7 @@ __global__ void __launch_bounds__(WPB * 32) arm_debug_kernel(const __grid_consta
   typename TK::TS T;
   real a_i;
   TK::load(A, W, io, env, lane, T, a_i);
-  typename E::ConReg C;
-  bool clamped = E::step1(A, W, lane, C);
-  typename E::SubOut so = E::step2(A, W, lane, C, clamped, a_i, T.time, false);
+  typename E::SubRes so = E::substep(&W, lane, a_i, T.time, 0);
   __syncwarp();
   constexpr int NV = WM::NV;
   if (lane == 0) {

@@ -128,6 +128,10 @@ class BatchedMujocoSimEnv:
         _lib.check(self._L.mjs_step_host(self._h, actions.ctypes.data_as(ctypes.c_void_p), obs.ctypes.data_as(ctypes.c_void_p),
                                          reward.ctypes.data_as(ctypes.c_void_p), flags.ctypes.data_as(ctypes.c_void_p), None, int(self.autoreset)))
 
+    def join_aux(self):
+        """Make the current stream wait for background reset preparation in flight."""
+        _lib.check(self._L.mjs_join_aux(self._h, self._stream()))
+
     # state injection / extraction for parity tests
     def set_state(self, states, first: int = 0, forward: bool = True):
         n = len(states)
