@@ -1,0 +1,353 @@
+"""bench.py -- env-steps/s of the Planar Push hot path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W          (N>1: launched by torchrun, one rank per GPU)
+    python bench.py --impl reference ...                   (CPU arm: the oracle port on the host cores)
+
+One "step" = one control step (20 physics substeps + task hooks + obs) of every env of the shard.
+Prints ONE JSON line on rank 0.  See DESIGN.md "Measurement" for how each field is produced.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name -> (task, default envs per GPU, algorithmic flops / env-step, algorithmic bytes / env-step)  
+    "planar_push": ("robot_planar_push", 4736, 0.86e6, 771.0),
+    "point_mass_reach": ("point_mass_reach", 65536, 3.6e3, 151.0),
+    "robot_reach": ("robot_reach", 16384, 0.115e6, 283.0),
+    "push_button": ("robot_push_button", 4736, 0.58e6, 539.0),
+}
+METRIC = "env-steps/s (device-timed) Planar Push"
+FP32_PEAK_TFLOPS_FALLBACK = 148 * 128 * 2 * 1.965e9 / 1e12  # SMs x FP32 lanes x FMA x clocks.max.sm = 74.4
+
+
+def _peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d.get("hbm_gbs", 6650.0)), "measured", float(d.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback", 1965.0
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Polls nvidia-smi (the recipe's clocks line) while the timed region runs."""
+
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index: int):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(r[3 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "power_w_max": max(float(r[2]) for r in self.rows),
+                "samples": len(self.rows), "reasons": reasons}
+
+
+# ----------------------------------------------------------------------------- CPU arm
+def _oracle_worker(bundle, states, actions, steps, tol_scale, out, idx):
+    import ctypes
+
+    from oracle.oracle import OracleEnvs
+
+    n = len(states)
+    ora = OracleEnvs(bundle, n)
+    ctypes.memmove(ora.states, states, ctypes.sizeof(states))
+    ora.tol_scale = tol_scale
+    t0 = time.perf_counter()
+    for k in range(steps):
+        ora.step_raw(actions[k])
+    out[idx] = time.perf_counter() - t0
+
+
+def cpu_oracle_rate(task: str, envs_per_core: int, steps: int, cores: int | None = None, seed: int = 0):
+    """Time the double-precision CPU oracle (oracle/mjs_oracle.cpp, MuJoCo's default solver tolerance)
+    on `cores` host threads (ctypes releases the GIL), `envs_per_core` envs each, `steps` control steps
+    of the same workload (same scene, same action box, settled initial states)."""
+    import mujoco_sim_b200.envs as _envs
+    from tests.helpers import copy_states, pointmass_states, push_states
+
+    cores = cores or len(os.sched_getaffinity(0))
+    bundle = _envs._BUILDERS[task]()
+    t = bundle.task
+    A = t.action_dim
+    n = envs_per_core * cores
+    if task == "robot_planar_push":
+        init = push_states(bundle, n, seed).states
+    elif task == "point_mass_reach":
+        init = pointmass_states(n, seed)
+    else:
+        raise SystemExit(f"cpu baseline: no host state generator for {task}")
+    rng = np.random.RandomState(seed + 1)
+    lo = np.array([t.action_lo[k] for k in range(A)]); hi = np.array([t.action_hi[k] for k in range(A)])
+    threads, out = [], [0.0] * cores
+    for c in range(cores):
+        chunk = copy_states((type(init[0]) * envs_per_core).from_address(__import__("ctypes").addressof(init) + c * envs_per_core * __import__("ctypes").sizeof(init[0])), envs_per_core)
+        acts = rng.uniform(lo, hi, (steps, envs_per_core, A))
+        threads.append(threading.Thread(target=_oracle_worker, args=(bundle, chunk, acts, steps, 1.0, out, c)))
+    t0 = time.perf_counter()
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    wall = time.perf_counter() - t0
+    return n * steps / wall, cores, f"{n} envs ({envs_per_core}/thread x {cores} threads) x {steps} control steps, {wall:.1f} s wall"
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def _dist_setup(n_gpus: int):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    elif n_gpus > 1:
+        raise SystemExit("--gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
+    return world, rank, local
+
+
+def _stagger_episodes(env, max_steps: int, seed: int):
+    """Spread the episode phase of the envs uniformly over [0, max_steps) so the timed region sees the
+    steady-state reset rate (1/max_steps per env-step) instead of zero resets."""
+    if max_steps <= 1:
+        return
+    st = env.get_state()
+    rng = np.random.RandomState(seed)
+    ph = rng.randint(0, max_steps, len(st))
+    for s, p in zip(st, ph):
+        s.episode_step = int(p)
+    env.set_state(st, forward=False)
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+
+    import mujoco_sim_b200 as ms
+
+    world, rank, local = _dist_setup(args.gpus)
+    task, n_default, flops_per, bytes_per = WORKLOADS[args.workload]
+    N = args.envs or n_default
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    env = ms.make(task, N, device=dev, seed=args.seed, env_offset=rank * N, precision=args.precision)
+    env.reset()
+    if task == "robot_planar_push":
+        _stagger_episodes(env, env.bundle.task.max_steps, args.seed + rank)
+    A, O = env.action_dim, env.obs_dim
+    lo = torch.tensor([env.bundle.task.action_lo[k] for k in range(A)], device=dev)
+    hi = torch.tensor([env.bundle.task.action_hi[k] for k in range(A)], device=dev)
+    g = torch.Generator(device=dev); g.manual_seed(args.seed + 17 * rank)
+    total = args.warmup + args.steps
+    ring = 16  # pre-generated action batches resident in HBM, reused cyclically
+    actions = (lo + (hi - lo) * torch.rand(ring, N, A, device=dev, generator=g)).float().contiguous()
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    stream = torch.cuda.current_stream(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed_region(step_fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(steps):
+            flush.zero_()          # L2 flush between timed iterations (inside the region: ~2% pessimistic)
+            step_fn(i)
+        env.join_aux()             # background reset preparation launched by these steps is part of the job
+        e1.record(stream)
+        barrier()
+        ms_ = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms_, op=dist.ReduceOp.MAX)
+        return float(ms_.item())
+
+    # ---- device-resident arm ("value")
+    for i in range(args.warmup):
+        env.step_flat(actions[i % ring])
+    l0 = env.launch_count
+    with ClockSampler(local) as clk:
+        t_ms = timed_region(lambda i: env.step_flat(actions[(args.warmup + i) % ring]), args.steps)
+    launches = env.launch_count - l0
+    # flush cost alone, for the record
+    barrier(); f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record(stream)
+    for _ in range(10):
+        flush.zero_()
+    f1.record(stream); torch.cuda.synchronize(dev)
+    flush_ms = f0.elapsed_time(f1) / 10
+    # ---- dominant kernel alone: per-launch duration with events on the launching stream, no flush
+    barrier()
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kn = max(3, min(args.steps, 20))
+    env.join_aux(); torch.cuda.synchronize(dev)
+    k0.record(stream)
+    for i in range(kn):
+        env.step_flat(actions[i % ring])
+    k1.record(stream); torch.cuda.synchronize(dev)
+    kernel_ms = k0.elapsed_time(k1) / kn
+
+    # ---- end-to-end arm: HOST buffers through the C-ABI host call (H2D + step + D2H + sync inside)
+    h_act = torch.empty(ring, N, A, dtype=torch.float32).pin_memory(); h_act.copy_(actions.cpu())
+    h_obs = torch.empty(N, O, dtype=torch.float32).pin_memory()
+    h_rew = torch.empty(N, dtype=torch.float32).pin_memory()
+    h_flg = torch.empty(N, 4, dtype=torch.uint8).pin_memory()
+    a_np, o_np, r_np, f_np = h_act.numpy(), h_obs.numpy(), h_rew.numpy(), h_flg.numpy()
+    for i in range(3):
+        env.step_host(a_np[i % ring], o_np, r_np, f_np)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        env.step_host(a_np[i % ring], o_np, r_np, f_np)
+    e2e_s = time.perf_counter() - t0
+    e2e_t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e_t.item())
+
+    # ---- episode statistics: the only collective of the path
+    stats = env.stats_tensor().clone()
+    if world > 1:
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+    stats = stats.cpu().tolist()
+
+    value = world * N * args.steps / (t_ms * 1e-3)
+    out = None
+    if rank == 0:
+        hbm_peak, peak_src, sm_max = _peaks()
+        kern_rate = N / (kernel_ms * 1e-3)
+        fp32_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12
+        out = {
+            "metric": METRIC if args.workload == "planar_push" else f"env-steps/s (device-timed) {args.workload}",
+            "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": t_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 dynamics/solver + f64 state integration" if args.precision == "mixed" else "f64",
+            "data": "synthetic (device reset kernel initial states, uniform random actions in the reachable workspace box)",
+            "config": {"workload": f"{args.workload}: UR5e + cylinder pusher + 3 cylinder props, 20 substeps/step, {N} envs/GPU",
+                       "envs_per_gpu": N, "precision": args.precision, "l2": f"flushed between timed iterations (256 MiB memset inside the region, {flush_ms:.3f} ms each)",
+                       "episodes": "phases staggered over [0,500): steady-state auto-reset rate"},
+            "e2e": {"value": world * N * args.steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": N * A * 4,
+                    "d2h_bytes_per_step": N * (O + 1) * 4 + N * 4},
+            "gpu_launches": int(launches),
+            "clocks": clk.summary(),
+            "roofline": {"bound": "fp32", "achieved": kern_rate * flops_per / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": kern_rate * flops_per / 1e12 / fp32_peak, "traffic": None,
+                         "kernel": "arm_step_kernel", "kernel_ms": kernel_ms, "flops_per_env_step": flops_per,
+                         "peak_source": f"148 SMs x 128 FP32 lanes x 2 x clocks.max.sm {sm_max:.0f} MHz (not in MEASURED_PEAKS.json; nominal)",
+                         "hbm": {"achieved": kern_rate * bytes_per / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": kern_rate * bytes_per / 1e9 / hbm_peak,
+                                 "peak_source": peak_src, "bytes_per_env_step": bytes_per}},
+            "episode_stats": dict(zip(["return_sum", "length_sum", "episodes", "successes", "truncations", "errors"], stats[:6])),
+        }
+    env.close()
+    return out, world, rank
+
+
+# ----------------------------------------------------------------------------- reference arm
+def run_reference(args):
+    """`--impl reference`: the reference's CPU path on the host cores.  The reference's arithmetic is
+    MuJoCo's C engine behind dm_control, neither vendored nor installed here or on the GPU box (no
+    network), so this times the repo's double-precision CPU restatement (oracle/, kind "port") with one
+    thread per host core.  Each step is a bounded sample (envs_per_core envs per thread)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return None
+    task = WORKLOADS[args.workload][0]
+    epc = args.cpu_envs_per_core
+    for _ in range(1):
+        cpu_oracle_rate(task, epc, max(1, min(args.warmup, 3)))  # warm-up (page-in, thread start)
+    rate, cores, sample = cpu_oracle_rate(task, epc, args.steps)
+    n = epc * cores
+    return {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * n / rate, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic (oracle-settled initial states, uniform random actions in the reachable workspace box)",
+        "config": {"workload": f"{args.workload}: UR5e + cylinder pusher + 3 cylinder props, 20 substeps/step; bounded sample of {n} envs per step",
+                   "note": "MuJoCo/dm_control unavailable on this box: CPU restatement (oracle port), Newton solver at MuJoCo's default tolerance 1e-8"},
+        "cpu_baseline": {"value": rate, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="planar_push", choices=list(WORKLOADS))
+    ap.add_argument("--envs", type=int, default=0, help="envs per GPU (default: the workload's)")
+    ap.add_argument("--precision", default="mixed", choices=["mixed", "f64"])
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-envs-per-core", type=int, default=32)
+    ap.add_argument("--cpu-steps", type=int, default=60)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        if args.steps > 200:
+            args.steps = 200  # keep the CPU arm within minutes
+        out = run_reference(args)
+        if out is not None:
+            print(json.dumps(out), flush=True)
+        return
+    args.warmup = max(args.warmup, 3)
+    out, world, rank = run_gpu(args)
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            task = WORKLOADS[args.workload][0]
+            rate, cores, sample = cpu_oracle_rate(task, args.cpu_envs_per_core, args.cpu_steps)
+            out["cpu_baseline"] = {"value": rate, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample}
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -66,6 +66,14 @@ class OracleEnvs:
         )
         return self.collect()
 
+    def step_raw(self, actions):
+        """step without gathering outputs into numpy (timed CPU baseline: no Python in the loop)"""
+        a = np.ascontiguousarray(actions, dtype=np.float64).reshape(self.n, self.task.action_dim)
+        lib().oracle_control_step(
+            ctypes.byref(self.model), ctypes.byref(self.task), self.states, _dp(a), self.outs, self.n,
+            ctypes.c_double(self.tol_scale), ctypes.byref(self.flops),
+        )
+
     def finish_reset(self, settle_steps: int = 0):
         lib().oracle_finish_reset(ctypes.byref(self.model), ctypes.byref(self.task), self.states, self.outs, self.n, settle_steps)
         return self.collect()
