@@ -70,3 +70,38 @@ def push_states(bundle, n, seed, settle=True):
         s.target[0], s.target[1], s.target[2] = rng.uniform(-0.15, 0.15), rng.uniform(-0.55, -0.35), 0.003
     ora.finish_reset(150 if settle else 0)
     return ora
+
+
+def arm_states(bundle, n, seed):
+    """Host-injected Robot Reach / Button Push states: IK'd spawn pose in the task's spawn box
+    (robot_reach.py:143-150, robot_push_button.py:126-134), target / switch position in its box."""
+    import ctypes
+
+    from oracle.oracle import OracleEnvs, _dp, lib
+
+    rng = np.random.RandomState(seed)
+    t = bundle.task
+    ora = OracleEnvs(bundle, n)
+    lo = np.array([t.spawn_lo[k] for k in range(3)]); hi = np.array([t.spawn_hi[k] for k in range(3)])
+    tlo = np.array([t.target_lo[k] for k in range(3)]); thi = np.array([t.target_hi[k] for k in range(3)])
+    button = bundle.name == "robot_push_button"
+    for e in range(n):
+        s = ora.states[e]
+        while True:
+            tcp = rng.uniform(lo, hi)
+            tgt = rng.uniform(tlo, thi)
+            if button:
+                tcp[2] = max(tcp[2], 0.12)  # start above the switch
+            q = np.zeros(6)
+            if lib().oracle_tcp_to_joints(ctypes.byref(t), _dp(tcp), _dp(np.zeros(6)), _dp(q)):
+                break
+        for i in range(6):
+            s.qpos[i] = q[i]
+            s.ctrl[i] = q[i]
+        for i in range(3):
+            if button:
+                s.ovr_pos[i] = tgt[i]
+            else:
+                s.target[i] = tgt[i]
+    ora.finish_reset(0)
+    return ora
