@@ -76,6 +76,10 @@ int mjs_join_aux(MjsSim* sim, void* stream);
  * stages (layout documented at arm_debug_kernel). */
 int mjs_debug_forward(MjsSim* sim, int env, double* h_out, int n);
 
+/* Test hook: continue the current control step of every env by k physics substeps (no before_step
+ * hook, no outputs), so tests can split a control step at a substep boundary. */
+int mjs_debug_substeps(MjsSim* sim, int k);
+
 /* Number of kernels this library launched since creation (bench `gpu_launches`). */
 long long mjs_launch_count(const MjsSim* sim);
 int mjs_num_envs(const MjsSim* sim);

@@ -68,14 +68,25 @@ static int launch(ArmSim* a, const ArmModel<real>& M, int which, ArmIO io, cudaS
     size_t smem_step = sizeof(WarpMem<real, NOBJ>) * WPBS;
     MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_step));
     k<<<(n + WPBS - 1) / WPBS, WPBS * 32, smem_step, st>>>(io);
+  } else if (which == 1 && first == 1) {
+    // refill (side stream, low priority): ONE warp per block so a refill block's shared memory fits next to
+    // a resident step block instead of taking a whole SM away from the step kernel for 150 substeps
+    auto k = arm_reset_kernel<real, NOBJ, 1>;
+    size_t smem1 = sizeof(WarpMem<real, NOBJ>);
+    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+    k<<<n, 32, smem1, st>>>(io, first);
   } else if (which == 1) {
     auto k = arm_reset_kernel<real, NOBJ, ARM_WPB>;
     MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k<<<grid, ARM_WPB * 32, smem, st>>>(io, first);
+  } else if (which == 4) {
+    auto k = arm_substeps_kernel<real, NOBJ, ARM_WPB>;
+    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid, ARM_WPB * 32, smem, st>>>(io, count);
   } else if (which == 3) {
     auto k = arm_debug_kernel<real, NOBJ, ARM_WPB>;
     MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<1, ARM_WPB * 32, smem, st>>>(io, first, a->d_debug);
+    k<<<1, ARM_WPB * 32, smem, st>>>(io, first, a->d_debug, count);
   } else {
     auto k = arm_forward_kernel<real, NOBJ, ARM_WPB>;
     MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -247,9 +258,17 @@ int arm_get_state(ArmSim* a, MjsEnvState* h, int first, int count) {
   return 0;
 }
 
+int arm_debug_substeps(ArmSim* a, int k) {
+  ArmIO io = make_io(a);
+  if (dispatch(a, 4, io, 0, 0, k) < 0) return -1;
+  MJS_CUDA_CHECK(cudaDeviceSynchronize());
+  return 0;
+}
+
 int arm_debug_forward(ArmSim* a, int env, double* h_out, int n) {
   ArmIO io = make_io(a);
-  if (dispatch(a, 3, io, 0, env, 1) < 0) return -1;
+  const char* pre = getenv("MJS_DEBUG_PRE");  // test hook: in-kernel substeps before the dumped forward pass
+  if (dispatch(a, 3, io, 0, env, pre ? atoi(pre) : 0) < 0) return -1;
   MJS_CUDA_CHECK(cudaDeviceSynchronize());
   MJS_CUDA_CHECK(cudaMemcpy(h_out, a->d_debug, sizeof(double) * (n < 1024 ? n : 1024), cudaMemcpyDeviceToHost));
   return 0;

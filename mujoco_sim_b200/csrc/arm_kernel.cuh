@@ -423,7 +423,7 @@ struct ArmEngine {
           real dist0 = dot3(dif, nrm);
           real vec[3] = {ax[0] * prjaxis - nrm[0], ax[1] * prjaxis - nrm[1], ax[2] * prjaxis - nrm[2]};
           real len_sqr = dot3(vec, vec);
-          if (len_sqr >= (real)(MJS_MINVAL * MJS_MINVAL)) {
+          if (len_sqr >= (real)(MJS_CYL_FLAT_TILT * MJS_CYL_FLAT_TILT)) {
             real s = s2[0] / sqrt(len_sqr);
             vec[0] *= s; vec[1] *= s; vec[2] *= s;
           } else {
@@ -1744,6 +1744,32 @@ __global__ void __launch_bounds__(WPB * 32) arm_reset_kernel(ArmIO io, int refil
   }
 }
 
+// Test hook (mjs_debug_substeps): continue the current control step by k physics substeps without
+// the before_step hook, so a control step can be split at a substep boundary.
+template <typename real, int NOBJ, int WPB>
+__global__ void __launch_bounds__(WPB * 32) arm_substeps_kernel(ArmIO io, int k) {
+  const ArmModel<real>& A = cmodel<real>();
+  using TK = ArmTask<real, NOBJ>;
+  using E = ArmEngine<real, NOBJ>;
+  using WM = WarpMem<real, NOBJ>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WM* wm = reinterpret_cast<WM*>(smem_raw);
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int e = blockIdx.x * WPB + warp;
+  if (e >= io.N) return;
+  WM& W = wm[warp];
+  typename TK::TS T;
+  real a_i;
+  TK::load(A, W, io, e, lane, T, a_i);
+  for (int i = 0; i < k; i++) {
+    TK::before_substep(A, W, lane, T);
+    typename E::SubRes so = E::substep(&W, lane, a_i, T.time, 1);
+    a_i = so.a_i; T.time = so.time;
+    if (A.kind == MJS_TASK_BUTTON) TK::switch_update(A, T, so.touch);
+  }
+  TK::store(W, io, e, lane, T, a_i);
+}
+
 // mj_forward on injected states (mjs_set_state with forward != 0): refresh the warm start
 template <typename real, int NOBJ, int WPB>
 __global__ void __launch_bounds__(WPB * 32) arm_forward_kernel(ArmIO io, int first, int count) {
@@ -1768,7 +1794,7 @@ __global__ void __launch_bounds__(WPB * 32) arm_forward_kernel(ArmIO io, int fir
 // debug: run mj_forward for one env and dump intermediate stages (tests only)
 //   out: [0..35] Marm, [36..36+NV) fsm, [..+NV) qacc, [..+NV) fcon, then ncon, then per contact (dist,pos3,normal3) x ncon, then link xpos (18), S (36)
 template <typename real, int NOBJ, int WPB>
-__global__ void __launch_bounds__(WPB * 32) arm_debug_kernel(ArmIO io, int env, double* out) {
+__global__ void __launch_bounds__(WPB * 32) arm_debug_kernel(ArmIO io, int env, double* out, int pre) {
   const ArmModel<real>& A = cmodel<real>();
   using TK = ArmTask<real, NOBJ>;
   using E = ArmEngine<real, NOBJ>;
@@ -1781,6 +1807,12 @@ __global__ void __launch_bounds__(WPB * 32) arm_debug_kernel(ArmIO io, int env, 
   typename TK::TS T;
   real a_i;
   TK::load(A, W, io, env, lane, T, a_i);
+  for (int i = 0; i < pre; i++) {  // continue the control step in-kernel first (no store)
+    TK::before_substep(A, W, lane, T);
+    typename E::SubRes s1 = E::substep(&W, lane, a_i, T.time, 1);
+    a_i = s1.a_i; T.time = s1.time;
+  }
+  if (pre) TK::before_substep(A, W, lane, T);
   typename E::SubRes so = E::substep(&W, lane, a_i, T.time, 0);
   __syncwarp();
   constexpr int NV = WM::NV;

@@ -7,6 +7,9 @@
 #include "../../include/mjs_model.h"
 
 #define MJS_MINVAL 1e-15
+// plane x cylinder: tilt (rad) below which the cylinder lies flat on the plane.  MuJoCo uses
+// mjMINVAL (1e-15), which rounding noise of a settled prop crosses at random; see DESIGN.md.
+#define MJS_CYL_FLAT_TILT 1e-9
 #define MJS_MINIMP 0.0001
 #define MJS_MAXIMP 0.9999
 #define MJS_MINMU 1e-5

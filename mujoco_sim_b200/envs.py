@@ -38,7 +38,7 @@ def _ptr(t: Optional[torch.Tensor]):
 
 class BatchedMujocoSimEnv:
     def __init__(self, task_name: str, num_envs: int, device="cuda:0", seed: int = 0, env_offset: int = 0,
-                 precision: str = "mixed", autoreset: bool = True, **task_kwargs):
+                 precision: str = "f64", autoreset: bool = True, **task_kwargs):
         if not torch.cuda.is_available():
             raise _lib.MjsimError("BatchedMujocoSimEnv needs a CUDA device (there is no CPU fallback)")
         self.bundle = _BUILDERS[task_name](**task_kwargs)
