@@ -25,7 +25,7 @@ import numpy as np  # noqa: E402
 
 WORKLOADS = {
     # name -> (task, default envs per GPU, algorithmic flops / env-step, algorithmic bytes / env-step)  
-    "planar_push": ("robot_planar_push", 4736, 0.86e6, 771.0),
+    "planar_push": ("robot_planar_push", 5328, 0.86e6, 771.0),   # 148 SMs x 12 FP64 warps x 3 waves
     "point_mass_reach": ("point_mass_reach", 65536, 3.6e3, 151.0),
     "robot_reach": ("robot_reach", 16384, 0.115e6, 283.0),
     "push_button": ("robot_push_button", 4736, 0.58e6, 539.0),
@@ -166,13 +166,16 @@ def run_gpu(args):
     import torch.distributed as dist
 
     import mujoco_sim_b200 as ms
+    from mujoco_sim_b200 import sharding
 
     world, rank, local = _dist_setup(args.gpus)
     task, n_default, flops_per, bytes_per = WORKLOADS[args.workload]
     N = args.envs or n_default
+    if not args.envs and task == "robot_planar_push" and args.precision == "mixed":
+        N = 4736  # 148 SMs x 16 FP32 warps x 2 waves
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
-    env = ms.make(task, N, device=dev, seed=args.seed, env_offset=rank * N, precision=args.precision)
+    env = ms.make(task, N, device=dev, seed=args.seed, env_offset=sharding.env_offset(rank, N), precision=args.precision)
     env.reset()
     if task == "robot_planar_push":
         _stagger_episodes(env, env.bundle.task.max_steps, args.seed + rank)
@@ -220,16 +223,19 @@ def run_gpu(args):
         flush.zero_()
     f1.record(stream); torch.cuda.synchronize(dev)
     flush_ms = f0.elapsed_time(f1) / 10
-    # ---- dominant kernel alone: per-launch duration with events on the launching stream, no flush
+    # ---- dominant kernel alone: per-launch duration, CUDA events on the launching stream around every launch
+    # (no flush); the median is robust against the low-priority refill kernel co-running on some launches
     barrier()
-    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    kn = max(3, min(args.steps, 20))
+    kn = max(5, min(args.steps, 40))
     env.join_aux(); torch.cuda.synchronize(dev)
-    k0.record(stream)
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(kn + 1)]
+    evs[0].record(stream)
     for i in range(kn):
         env.step_flat(actions[i % ring])
-    k1.record(stream); torch.cuda.synchronize(dev)
-    kernel_ms = k0.elapsed_time(k1) / kn
+        evs[i + 1].record(stream)
+    torch.cuda.synchronize(dev)
+    per = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(kn))
+    kernel_ms = per[len(per) // 2]
 
     # ---- end-to-end arm: HOST buffers through the C-ABI host call (H2D + step + D2H + sync inside)
     h_act = torch.empty(ring, N, A, dtype=torch.float32).pin_memory(); h_act.copy_(actions.cpu())
@@ -253,31 +259,32 @@ def run_gpu(args):
     # Not the headline: it misses the 1e-4 single-step gate on impact steps (tests/test_arm_gpu.py).
     alt = None
     if args.precision == "f64" and not args.no_alt:
-        env2 = ms.make(task, N, device=dev, seed=args.seed, env_offset=rank * N, precision="mixed")
+        N2 = N if args.envs else 4736
+        env2 = ms.make(task, N2, device=dev, seed=args.seed, env_offset=rank * N, precision="mixed")
         env2.reset()
         if task == "robot_planar_push":
             _stagger_episodes(env2, env2.bundle.task.max_steps, args.seed + rank)
+        act2 = actions[:, :N2].contiguous() if N2 <= N else (lo + (hi - lo) * torch.rand(ring, N2, A, device=dev, generator=g)).float()
         for i in range(args.warmup):
-            env2.step_flat(actions[i % ring])
+            env2.step_flat(act2[i % ring])
         main_env, env = env, env2
-        t2 = timed_region(lambda i: env2.step_flat(actions[(args.warmup + i) % ring]), args.steps)
+        t2 = timed_region(lambda i: env2.step_flat(act2[(args.warmup + i) % ring]), args.steps)
         env = main_env
         env2.close()
-        alt = {"precision": "mixed", "value": world * N * args.steps / (t2 * 1e-3), "unit": "env-steps/s", "ms_per_step": t2 / args.steps,
+        alt = {"precision": "mixed", "envs_per_gpu": N2, "value": world * N2 * args.steps / (t2 * 1e-3), "unit": "env-steps/s", "ms_per_step": t2 / args.steps,
                "note": "FP32 dynamics/solver + FP64 state; misses the 1e-4 single-step gate on impact steps, reported only"}
 
     # ---- episode statistics: the only collective of the path
-    stats = env.stats_tensor().clone()
-    if world > 1:
-        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
-    stats = stats.cpu().tolist()
+    stats = sharding.allreduce_stats(env.stats_tensor())
 
     value = world * N * args.steps / (t_ms * 1e-3)
     out = None
     if rank == 0:
         hbm_peak, peak_src, sm_max = _peaks()
         kern_rate = N / (kernel_ms * 1e-3)
-        fp32_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12
+        lanes = 64 if args.precision == "f64" else 128  # FP64 issues at half the FP32 rate on B200
+        fp32_peak = 148 * lanes * 2 * sm_max * 1e6 / 1e12
+        bound = "fp64" if args.precision == "f64" else "fp32"
         out = {
             "metric": METRIC if args.workload == "planar_push" else f"env-steps/s (device-timed) {args.workload}",
             "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -291,14 +298,14 @@ def run_gpu(args):
                     "d2h_bytes_per_step": N * (O + 1) * 4 + N * 4},
             "gpu_launches": int(launches),
             "clocks": clk.summary(),
-            "roofline": {"bound": "fp32", "achieved": kern_rate * flops_per / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
+            "roofline": {"bound": bound, "achieved": kern_rate * flops_per / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": kern_rate * flops_per / 1e12 / fp32_peak, "traffic": None,
                          "kernel": "arm_step_kernel", "kernel_ms": kernel_ms, "flops_per_env_step": flops_per,
-                         "peak_source": f"148 SMs x 128 FP32 lanes x 2 x clocks.max.sm {sm_max:.0f} MHz (not in MEASURED_PEAKS.json; nominal)",
+                         "peak_source": f"148 SMs x {lanes} {bound.upper()} lanes x 2 x clocks.max.sm {sm_max:.0f} MHz, nominal non-tensor FMA peak (MEASURED_PEAKS.json has only HBM and bf16 tensor peaks)",
                          "hbm": {"achieved": kern_rate * bytes_per / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": kern_rate * bytes_per / 1e9 / hbm_peak,
                                  "peak_source": peak_src, "bytes_per_env_step": bytes_per}},
             "alt_precision": alt,
-            "episode_stats": dict(zip(["return_sum", "length_sum", "episodes", "successes", "truncations", "errors"], stats[:6])),
+            "episode_stats": {k: stats[k] for k in sharding.STAT_KEYS[:6]},
         }
     env.close()
     return out, world, rank

@@ -78,8 +78,8 @@ static int build_pm_params(const MjsModel& m, const MjsTask& t, PmParams<real>& 
   P.n_sub = t.n_sub; P.reward_type = t.reward_type;
   P.scale = (real)(1.0 / (m.meaninertia * 2));
   P.max_iter = m.solver_iterations;
-  // all-double runs iterate to the oracle's tolerance; FP32 stops at what FP32 can resolve
-  P.tol = sizeof(real) == 8 ? (real)(m.tolerance * 1e-4) : (real)1e-7;
+  // mjOption.tolerance as given (parity tests pass 1e-12 to both sides); FP32 stops at what FP32 can resolve
+  P.tol = sizeof(real) == 8 ? (real)m.tolerance : (real)(m.tolerance > 1e-7 ? m.tolerance : 1e-7);
   P.body_x = (real)m.body_pos[3 * b]; P.body_y = (real)m.body_pos[3 * b + 1];
   double bz = m.body_pos[3 * b + 2];
   P.weld_relx = (real)m.eq_data[3]; P.weld_rely = (real)m.eq_data[4];

@@ -2,107 +2,13 @@
 #include <cstdlib>
 #include <vector>
 
-#include "arm_api.cuh"
-#include "arm_kernel.cuh"
-
-#define ARM_WPB 4  // warps (= envs) per thread block (reset / forward / debug kernels)
-// Step kernel: one block of ARM_STEP_WPB warps per SM running the substep stages in
-// lock-step (barriers between stages) so the warps share their instruction fetches.
-#ifndef ARM_STEP_WPB
-#define ARM_STEP_WPB 16
-#endif
-#ifndef ARM_STEP_SYNC
-#define ARM_STEP_SYNC true
-#endif
-
-struct ArmSim {
-  int N, nobj, precision;
-  unsigned long long seed;
-  unsigned int env_offset;
-  double* d_stats;
-  double* sd;
-  int* si;
-  int SD, SI;
-  ArmModel<float> mf;
-  ArmModel<double> md;
-  double* d_debug;
-  // pre-settled reset slots + side stream (tasks with settle steps)
-  double* slot_sd;
-  int* slot_si;
-  float* slot_obs;
-  int* slot_ready;
-  cudaStream_t side;
-  cudaEvent_t ev_step, ev_refill;
-  int refill_pending;
-  long long extra_launches;
-};
+#include "arm_sim.cuh"
 
 template <int NOBJ>
 static void layout_sizes(int& sd, int& si) { sd = ArmLayout<NOBJ>::SD; si = ArmLayout<NOBJ>::SI; }
 
-// The kernels read the model from the __constant__ block c_arm_model.  It is
-// re-uploaded (after a device sync) whenever a different simulator or precision
-// launches on this device, so several simulators may coexist in a process.
-static const void* g_const_owner[64];
-template <typename real>
-static int bind_model(const ArmModel<real>& M) {
-  int dev = 0;
-  MJS_CUDA_CHECK(cudaGetDevice(&dev));
-  if (g_const_owner[dev & 63] == (const void*)&M) return 0;
-  MJS_CUDA_CHECK(cudaDeviceSynchronize());
-  MJS_CUDA_CHECK(cudaMemcpyToSymbol(c_arm_model, &M, sizeof(M)));
-  g_const_owner[dev & 63] = (const void*)&M;
-  return 0;
-}
-
-template <typename real, int NOBJ>
-static int launch(ArmSim* a, const ArmModel<real>& M, int which, ArmIO io, cudaStream_t st, int first = 0, int count = 0) {
-  if (bind_model<real>(M)) return -1;
-  size_t smem = sizeof(WarpMem<real, NOBJ>) * ARM_WPB;
-  int n = which == 2 ? count : a->N;
-  int grid = (n + ARM_WPB - 1) / ARM_WPB;
-  if (which == 0) {
-    // doubles need twice the shared memory: half the warps per block
-    constexpr int WPBS = sizeof(real) == 8 ? ARM_STEP_WPB / 2 : ARM_STEP_WPB;
-    auto k = arm_step_kernel<real, NOBJ, WPBS, ARM_STEP_SYNC>;
-    size_t smem_step = sizeof(WarpMem<real, NOBJ>) * WPBS;
-    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_step));
-    k<<<(n + WPBS - 1) / WPBS, WPBS * 32, smem_step, st>>>(io);
-  } else if (which == 1 && first == 1) {
-    // refill (side stream, low priority): ONE warp per block so a refill block's shared memory fits next to
-    // a resident step block instead of taking a whole SM away from the step kernel for 150 substeps
-    auto k = arm_reset_kernel<real, NOBJ, 1>;
-    size_t smem1 = sizeof(WarpMem<real, NOBJ>);
-    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
-    k<<<n, 32, smem1, st>>>(io, first);
-  } else if (which == 1) {
-    auto k = arm_reset_kernel<real, NOBJ, ARM_WPB>;
-    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<grid, ARM_WPB * 32, smem, st>>>(io, first);
-  } else if (which == 4) {
-    auto k = arm_substeps_kernel<real, NOBJ, ARM_WPB>;
-    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<grid, ARM_WPB * 32, smem, st>>>(io, count);
-  } else if (which == 3) {
-    auto k = arm_debug_kernel<real, NOBJ, ARM_WPB>;
-    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<1, ARM_WPB * 32, smem, st>>>(io, first, a->d_debug, count);
-  } else {
-    auto k = arm_forward_kernel<real, NOBJ, ARM_WPB>;
-    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<grid, ARM_WPB * 32, smem, st>>>(io, first, count);
-  }
-  MJS_CUDA_CHECK(cudaGetLastError());
-  return 1;
-}
-
 static int dispatch(ArmSim* a, int which, ArmIO io, cudaStream_t st, int first = 0, int count = 0) {
-  bool f64 = a->precision == 0;
-  switch (a->nobj) {
-    case 0: return f64 ? launch<double, 0>(a, a->md, which, io, st, first, count) : launch<float, 0>(a, a->mf, which, io, st, first, count);
-    case 3: return f64 ? launch<double, 3>(a, a->md, which, io, st, first, count) : launch<float, 3>(a, a->mf, which, io, st, first, count);
-    default: mjs_set_error("arm engine: built for 0 or 3 props, got %d", a->nobj); return -1;
-  }
+  return a->precision == 0 ? arm_launch_f64(a, which, io, st, first, count) : arm_launch_f32(a, which, io, st, first, count);
 }
 
 ArmSim* arm_create(const MjsModel& m, const MjsTask& t, int N, unsigned long long seed, unsigned int env_offset, int precision, double* d_stats) {
@@ -139,7 +45,7 @@ ArmSim* arm_create(const MjsModel& m, const MjsTask& t, int N, unsigned long lon
 
 void arm_destroy(ArmSim* a) {
   if (!a) return;
-  for (int d = 0; d < 64; d++) if (g_const_owner[d] == (const void*)&a->mf || g_const_owner[d] == (const void*)&a->md) g_const_owner[d] = nullptr;
+  arm_forget_f32(a); arm_forget_f64(a);
   cudaFree(a->sd); cudaFree(a->si); cudaFree(a->d_debug);
   if (a->slot_ready) {
     cudaStreamSynchronize(a->side);

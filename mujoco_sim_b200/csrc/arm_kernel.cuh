@@ -19,6 +19,15 @@
 #include "arm_model.cuh"
 
 #define FULLMASK 0xffffffffu
+// warps per lock-step group (must divide the warps per block of the step kernel).  Measured on B200,
+// Planar Push: FP64 12 warps/block: group 12 -> 1.30 M env-steps/s kernel-only, 6 -> 1.36 M, 4/3/2 -> 1.36-1.37 M but
+// worse once the refill kernel co-runs; FP32 16 warps/block: 16 -> 1.59 M, 4 -> 1.42 M, 2 -> 1.30 M.
+#ifndef ARM_SYNC_GROUP_F64
+#define ARM_SYNC_GROUP_F64 6
+#endif
+#ifndef ARM_SYNC_GROUP_F32
+#define ARM_SYNC_GROUP_F32 16
+#endif
 
 // The specialised model lives in constant memory: every stage reads it as
 // constant-bank operands, and the heavy per-substep code can be one
@@ -48,11 +57,12 @@ struct WarpMem {
   real cf[4][CS];               // contact-space force of the current iterate
   real cW[7][CS];               // arrow Hessian weights: W00, W01..W03, W11..W33
   real craw[10][CS];            // dist, pos[3], normal[3], yhint[3]
-  int cpair[ARM_MAXC];
-  int cblk[2][ARM_MAXC];        // dof block of side 0/1: -1 none, 0 arm, 1+k prop k
-  int ccols[2][ARM_MAXC];       // number of arm columns (link+1) when the side is the arm
+  // small integer tables are narrow on purpose: 12 FP64 warps must fit in 227 KB of shared memory
+  short cpair[ARM_MAXC];
+  signed char cblk[2][ARM_MAXC];        // dof block of side 0/1: -1 none, 0 arm, 1+k prop k
+  unsigned char ccols[2][ARM_MAXC];     // number of arm columns (link+1) when the side is the arm
   int bcount[1 + ARM_MAXOBJ];
-  int blist[1 + ARM_MAXOBJ][ARM_MAXCB];  // contact | side<<8
+  unsigned short blist[1 + ARM_MAXOBJ][ARM_MAXCB];  // contact | side<<8
   int ncon;
   int status;
   int sync;     // lock-step mode: all warps of the block pass the stage barriers together
@@ -80,7 +90,8 @@ template <> __device__ __forceinline__ void sincos_r<float>(float x, float* s, f
 template <> __device__ __forceinline__ void sincos_r<double>(double x, double* s, double* c) { sincos(x, s, c); }
 template <typename real> __device__ __forceinline__ real rsqrt_r(real x);
 template <> __device__ __forceinline__ float rsqrt_r<float>(float x) { return rsqrtf(x); }
-template <> __device__ __forceinline__ double rsqrt_r<double>(double x) { return 1.0 / sqrt(x); }
+// rsqrt(double): MUFU.RSQ64H seed + Newton steps (~1 ulp), a quarter of the instructions of 1.0 / sqrt(x)
+template <> __device__ __forceinline__ double rsqrt_r<double>(double x) { return rsqrt(x); }
 
 template <typename real>
 __device__ __forceinline__ void cross3(real* r, const real* a, const real* b) {
@@ -159,7 +170,21 @@ struct ArmEngine {
   // (L1.5 = 32 KB) and has almost no temporal reuse inside a warp, so warps that
   // drift apart all stream their own instructions from L2.  Barriers between the
   // stages keep the warps of a block inside the same code window.
-  __device__ static __forceinline__ void stage_sync(const WM& W, int level = 2) { if (W.sync >= level) __syncthreads(); }
+  // Barriers are per lock-step GROUP of ARM_SYNC_GROUP warps (named barriers 1..15), not per block: warps
+  // that wait for the slowest member of their group lose less when the group is smaller, at the price of
+  // sharing instruction fetches among fewer warps.
+  static constexpr int SYNC_GROUP = sizeof(real) == 8 ? ARM_SYNC_GROUP_F64 : ARM_SYNC_GROUP_F32;
+  __device__ static __forceinline__ void group_sync() {
+    int id = 1 + (threadIdx.x >> 5) / SYNC_GROUP;
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(SYNC_GROUP * 32) : "memory");
+  }
+  __device__ static __forceinline__ bool group_or(bool pred) {
+    int id = 1 + (threadIdx.x >> 5) / SYNC_GROUP, r;
+    asm volatile("{ .reg .pred p, q; setp.ne.s32 p, %1, 0; bar.red.or.pred q, %2, %3, p; selp.s32 %0, 1, 0, q; }"
+                 : "=r"(r) : "r"((int)pred), "r"(id), "r"(SYNC_GROUP * 32) : "memory");
+    return r != 0;
+  }
+  __device__ static __forceinline__ void stage_sync(const WM& W, int level = 2) { if (W.sync >= level) group_sync(); }
 
   // ------------------------------------------------------------- [P1] kinematics
   // Restates mj_kinematics for the chain/free-body structure.  Leaves xpos/xmat of
@@ -982,7 +1007,7 @@ struct ArmEngine {
         prev_cost = cost;
       }
       // lock-step mode: the block leaves the loop together (shared instruction fetch)
-      if (W.sync) { if (!__syncthreads_or(!done)) break; }
+      if (W.sync) { if (!group_or(!done)) break; }
       else if (done) break;
       if (!done) {
         nit++;

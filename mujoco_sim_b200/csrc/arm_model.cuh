@@ -307,7 +307,8 @@ int build_arm_model(const MjsModel& m, const MjsTask& t, int precision_f64, ArmM
   A.action_dim = t.action_dim; A.obs_dim = t.obs_dim; A.integrator = m.integrator; A.max_iter = m.solver_iterations;
   A.timestep = (real)m.timestep; A.impratio = (real)m.impratio;
   A.scale = (real)(1.0 / (m.meaninertia * (m.nv > 1 ? m.nv : 1)));
-  A.tol = precision_f64 ? (real)(m.tolerance * 1e-4) : (real)1e-6;
+  // mjOption.tolerance as given (MuJoCo default 1e-8; parity tests pass 1e-12 to both sides); FP32 cannot resolve below 1e-6
+  A.tol = precision_f64 ? (real)m.tolerance : (real)(m.tolerance > 1e-6 ? m.tolerance : 1e-6);
   for (int k = 0; k < 3; k++) A.gravity[k] = (real)m.gravity[k];
   A.control_dt = t.control_dt; A.time_limit = t.time_limit; A.goal_threshold = t.goal_threshold; A.target_radius = t.target_radius;
   A.nearest_coef = t.nearest_coef; A.tcp_z = t.tcp_z; A.obj_radius = t.obj_radius;

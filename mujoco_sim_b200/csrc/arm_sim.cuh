@@ -1,0 +1,48 @@
+// arm_sim.cuh -- host-side simulator record of the articulated engine, shared by arm.cu (state
+// management) and the per-precision launch units arm_f32.cu / arm_f64.cu (compiled in parallel).
+#pragma once
+#include "arm_api.cuh"
+#include "arm_kernel.cuh"
+
+#define ARM_WPB 4  // warps (= envs) per thread block (reset / forward / debug kernels)
+// Step kernel: one block of ARM_STEP_WPB warps per SM running the substep stages in
+// lock-step (barriers between stages) so the warps share their instruction fetches.
+#ifndef ARM_STEP_WPB
+#define ARM_STEP_WPB 16
+#endif
+#ifndef ARM_STEP_WPB_F64
+#define ARM_STEP_WPB_F64 12  // 12 x 19.3 KB of FP64 WarpMem fill the 227 KB of one SM; 168 regs x 384 threads fit the RF
+#endif
+#ifndef ARM_STEP_SYNC
+#define ARM_STEP_SYNC true
+#endif
+
+struct ArmSim {
+  int N, nobj, precision;
+  unsigned long long seed;
+  unsigned int env_offset;
+  double* d_stats;
+  double* sd;
+  int* si;
+  int SD, SI;
+  ArmModel<float> mf;
+  ArmModel<double> md;
+  double* d_debug;
+  // pre-settled reset slots + side stream (tasks with settle steps)
+  double* slot_sd;
+  int* slot_si;
+  float* slot_obs;
+  int* slot_ready;
+  cudaStream_t side;
+  cudaEvent_t ev_step, ev_refill;
+  int refill_pending;
+  long long extra_launches;
+};
+
+
+// per-precision launch units: run kernel `which` (0 step, 1 reset/refill, 2 forward, 3 debug, 4 substeps);
+// return the number of kernels launched or a negative error
+int arm_launch_f32(ArmSim* a, int which, ArmIO io, cudaStream_t st, int first, int count);
+int arm_launch_f64(ArmSim* a, int which, ArmIO io, cudaStream_t st, int first, int count);
+void arm_forget_f32(ArmSim* a);
+void arm_forget_f64(ArmSim* a);

@@ -38,10 +38,14 @@ def _ptr(t: Optional[torch.Tensor]):
 
 class BatchedMujocoSimEnv:
     def __init__(self, task_name: str, num_envs: int, device="cuda:0", seed: int = 0, env_offset: int = 0,
-                 precision: str = "f64", autoreset: bool = True, **task_kwargs):
+                 precision: str = "f64", autoreset: bool = True, solver_tolerance: Optional[float] = None, **task_kwargs):
         if not torch.cuda.is_available():
             raise _lib.MjsimError("BatchedMujocoSimEnv needs a CUDA device (there is no CPU fallback)")
         self.bundle = _BUILDERS[task_name](**task_kwargs)
+        model = type(self.bundle.model)()
+        ctypes.memmove(ctypes.byref(model), ctypes.byref(self.bundle.model), ctypes.sizeof(model))
+        if solver_tolerance is not None:  # mjOption.tolerance of the Newton solver (MuJoCo default 1e-8)
+            model.tolerance = float(solver_tolerance)
         self.task_name = task_name
         self.num_envs = int(num_envs)
         self.device = torch.device(device)
@@ -50,7 +54,7 @@ class BatchedMujocoSimEnv:
         self._h = ctypes.c_void_p()
         prec = {"f64": _lib.PRECISION_F64, "mixed": _lib.PRECISION_MIXED}[precision]
         dev_index = self.device.index or 0
-        _lib.check(self._L.mjs_create(ctypes.byref(self.bundle.model), ctypes.byref(self.bundle.task), self.num_envs, dev_index,
+        _lib.check(self._L.mjs_create(ctypes.byref(model), ctypes.byref(self.bundle.task), self.num_envs, dev_index,
                                       int(seed) & (2**64 - 1), int(env_offset), prec, ctypes.byref(self._h)))
         N, O, A = self.num_envs, self.bundle.task.obs_dim, self.bundle.task.action_dim
         self.obs_dim, self.action_dim = O, A

@@ -6,13 +6,15 @@ visible, constructing a simulator raises.
 from __future__ import annotations
 
 import ctypes
+import os
 import subprocess
 from pathlib import Path
 
 from .model.cstruct import MjsEnvState, MjsModel, MjsTask
 
 _PKG = Path(__file__).resolve().parent
-LIB_PATH = _PKG / "libmjsim_b200.so"
+# MJS_LIB: tuning experiments load an alternative build of the same library
+LIB_PATH = Path(os.environ["MJS_LIB"]).resolve() if os.environ.get("MJS_LIB") else _PKG / "libmjsim_b200.so"
 
 PRECISION_F64 = 0
 PRECISION_MIXED = 1
@@ -24,7 +26,7 @@ class MjsimError(RuntimeError):
 
 def build(force: bool = False, verbose: bool = False):
     """Compile libmjsim_b200.so in-tree with nvcc for sm_100a (no GPU needed)."""
-    args = ["make", "-C", str(_PKG / "csrc")]
+    args = ["make", "-j6", "-C", str(_PKG / "csrc")]
     if not verbose:
         args.append("-s")
     if force:

@@ -24,8 +24,8 @@ def _env(task, n, prec, bundle=None):
 
     if bundle is not None:
         ms.envs.register_builder("_test_" + task, lambda: bundle)
-        return ms.BatchedMujocoSimEnv("_test_" + task, n, precision=prec, autoreset=False)
-    return ms.BatchedMujocoSimEnv(task, n, precision=prec, autoreset=False)
+        return ms.BatchedMujocoSimEnv("_test_" + task, n, precision=prec, autoreset=False, solver_tolerance=1e-12)
+    return ms.BatchedMujocoSimEnv(task, n, precision=prec, autoreset=False, solver_tolerance=1e-12)
 
 
 def _qv(env, nq, nv):

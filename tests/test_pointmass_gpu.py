@@ -29,13 +29,13 @@ def _rollout(precision, n=1024, steps=200, seed=0):
     init = pointmass_states(n, seed)
     ctypes.memmove(ora.states, init, ctypes.sizeof(init))
     ora.finish_reset()
-    env = ms.BatchedMujocoSimEnv("point_mass_reach", n, precision=precision, autoreset=False)
+    env = ms.BatchedMujocoSimEnv("point_mass_reach", n, precision=precision, autoreset=False, solver_tolerance=1e-12)
     env.bundle.task.time_limit = 0.0
     env.close()
     # re-create with the patched task (time limit disabled)
     env = ms.BatchedMujocoSimEnv.__new__(ms.BatchedMujocoSimEnv)
     ms.envs.register_builder("_pm_nolimit", lambda: bundle)
-    env.__init__("_pm_nolimit", n, precision=precision, autoreset=False)
+    env.__init__("_pm_nolimit", n, precision=precision, autoreset=False, solver_tolerance=1e-12)
     env.set_state(copy_states(ora.states, n))
     rng = np.random.RandomState(seed + 1)
     worst_q = worst_v = 0.0
