@@ -188,6 +188,13 @@ def run_gpu(args):
     actions = (lo + (hi - lo) * torch.rand(ring, N, A, device=dev, generator=g)).float().contiguous()
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = torch.cuda.current_stream(dev)
+    host_actions = args.workload == "planar_push"
+    if not host_actions:
+        # the other workloads draw their synthetic actions on the device (Philox; Button Push: q_now +- 0.05 rad,
+        # SURVEY.md 8d) -- mjs_step(actions = NULL); e2e still copies results to the host every step
+        class _NoneRing:
+            def __getitem__(self, i): return None
+        actions = _NoneRing()
 
     def barrier():
         if world > 1:
@@ -238,17 +245,19 @@ def run_gpu(args):
     kernel_ms = per[len(per) // 2]
 
     # ---- end-to-end arm: HOST buffers through the C-ABI host call (H2D + step + D2H + sync inside)
-    h_act = torch.empty(ring, N, A, dtype=torch.float32).pin_memory(); h_act.copy_(actions.cpu())
+    h_act = torch.empty(ring, N, A, dtype=torch.float32).pin_memory()
+    if host_actions:
+        h_act.copy_(actions.cpu())
     h_obs = torch.empty(N, O, dtype=torch.float32).pin_memory()
     h_rew = torch.empty(N, dtype=torch.float32).pin_memory()
     h_flg = torch.empty(N, 4, dtype=torch.uint8).pin_memory()
     a_np, o_np, r_np, f_np = h_act.numpy(), h_obs.numpy(), h_rew.numpy(), h_flg.numpy()
     for i in range(3):
-        env.step_host(a_np[i % ring], o_np, r_np, f_np)
+        env.step_host(a_np[i % ring] if host_actions else None, o_np, r_np, f_np)
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
-        env.step_host(a_np[i % ring], o_np, r_np, f_np)
+        env.step_host(a_np[i % ring] if host_actions else None, o_np, r_np, f_np)
     e2e_s = time.perf_counter() - t0
     e2e_t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
     if world > 1:
@@ -258,7 +267,7 @@ def run_gpu(args):
     # ---- secondary: the FP32-dynamics variant (precision="mixed"), same workload and timing method.
     # Not the headline: it misses the 1e-4 single-step gate on impact steps (tests/test_arm_gpu.py).
     alt = None
-    if args.precision == "f64" and not args.no_alt:
+    if args.precision == "f64" and not args.no_alt and host_actions:
         N2 = N if args.envs else 4736
         env2 = ms.make(task, N2, device=dev, seed=args.seed, env_offset=rank * N, precision="mixed")
         env2.reset()
@@ -291,10 +300,11 @@ def run_gpu(args):
             "ms_per_step": t_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 dynamics/solver + f64 state integration" if args.precision == "mixed" else "f64",
             "data": "synthetic (device reset kernel initial states, uniform random actions in the reachable workspace box)",
-            "config": {"workload": f"{args.workload}: UR5e + cylinder pusher + 3 cylinder props, 20 substeps/step, {N} envs/GPU",
+            "config": {"workload": (f"{args.workload}: UR5e + cylinder pusher + 3 cylinder props, 20 substeps/step, {N} envs/GPU" if host_actions
+                                    else f"{args.workload}: {env.bundle.task.n_sub} substeps/step, {N} envs/GPU, device-drawn actions"),
                        "envs_per_gpu": N, "precision": args.precision, "l2": f"flushed between timed iterations (256 MiB memset inside the region, {flush_ms:.3f} ms each)",
                        "episodes": "phases staggered over [0,500): steady-state auto-reset rate"},
-            "e2e": {"value": world * N * args.steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": N * A * 4,
+            "e2e": {"value": world * N * args.steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": N * A * 4 if host_actions else 0,
                     "d2h_bytes_per_step": N * (O + 1) * 4 + N * 4},
             "gpu_launches": int(launches),
             "clocks": clk.summary(),
@@ -305,7 +315,7 @@ def run_gpu(args):
                          "hbm": {"achieved": kern_rate * bytes_per / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": kern_rate * bytes_per / 1e9 / hbm_peak,
                                  "peak_source": peak_src, "bytes_per_env_step": bytes_per}},
             "alt_precision": alt,
-            "episode_stats": {k: stats[k] for k in sharding.STAT_KEYS[:6]},
+            "episode_stats": {k: stats[k] for k in sharding.STAT_KEYS},
         }
     env.close()
     return out, world, rank
@@ -363,7 +373,7 @@ def main():
     args.warmup = max(args.warmup, 3)
     out, world, rank = run_gpu(args)
     if rank == 0:
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and args.workload in ("planar_push", "point_mass_reach"):
             task = WORKLOADS[args.workload][0]
             rate, cores, sample = cpu_oracle_rate(task, args.cpu_envs_per_core, args.cpu_steps)
             out["cpu_baseline"] = {"value": rate, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample}

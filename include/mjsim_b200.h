@@ -63,7 +63,7 @@ int mjs_get_state(MjsSim* sim, MjsEnvState* h_states, int first, int count);
 
 /* Episode statistics accumulated by the step kernel since the last call
  * (SURVEY.md 8e): {return sum, length sum, episodes, successes, truncations,
- * errors, env-steps, 0}.  d_out may be fed to an NCCL all-reduce directly. */
+ * errors, physics substeps, Newton iterations}.  d_out may be fed to an NCCL all-reduce directly. */
 int mjs_stats_device(MjsSim* sim, double** d_out);
 int mjs_stats(MjsSim* sim, double* h_out8, int reset);
 

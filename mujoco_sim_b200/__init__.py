@@ -4,3 +4,4 @@ Drop-in scope: the per-control-step hot path behind
 /root/reference/mujoco_sim/environments/dmc2gym.py (DMCEnvironmentAdapter).
 """
 from .envs import BatchedMujocoSimEnv, make  # noqa: F401
+from .vecenv import GymnasiumVectorFacade, SB3VecEnvFacade, make_vec  # noqa: F401

@@ -58,7 +58,7 @@ void arm_destroy(ArmSim* a) {
 static ArmIO make_io(ArmSim* a) {
   ArmIO io;
   memset(&io, 0, sizeof(io));
-  { const char* lv = getenv("MJS_SYNC_LEVEL"); io.sync_level = lv ? atoi(lv) : 1; }
+  { const char* lv = getenv("MJS_SYNC_LEVEL"); io.sync_level = lv ? atoi(lv) : 2; /* 1: barrier at substep start; 2: + before the solve and per Newton iteration; 3: every stage */ }
   io.sd = a->sd; io.si = a->si; io.stats = a->d_stats;
   io.slot_sd = a->slot_sd; io.slot_si = a->slot_si; io.slot_obs = a->slot_obs; io.slot_ready = a->slot_ready; io.N = a->N; io.seed = a->seed; io.env_offset = a->env_offset;
   return io;

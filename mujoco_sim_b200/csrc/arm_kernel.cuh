@@ -1007,7 +1007,7 @@ struct ArmEngine {
         prev_cost = cost;
       }
       // lock-step mode: the block leaves the loop together (shared instruction fetch)
-      if (W.sync) { if (!group_or(!done)) break; }
+      if (W.sync >= 2) { if (!group_or(!done)) break; }
       else if (done) break;
       if (!done) {
         nit++;
@@ -1043,7 +1043,7 @@ struct ArmEngine {
         }
         __syncwarp();
       }
-      stage_sync(W);
+      stage_sync(W, 3);
       if (!done) {
         real b = -grad;
         if (W.objcoup == 0) b = block_direction(W, lane, b);
@@ -1052,7 +1052,7 @@ struct ArmEngine {
         if (isdof) W.dir[lane] = dir_i;
         __syncwarp();
       }
-      stage_sync(W);
+      stage_sync(W, 3);
       if (!done) {
         // ---- exact line search along dir
         real Md = 0;
@@ -1227,17 +1227,17 @@ struct ArmEngine {
     ConReg C;
     stage_sync(W, 1);
     kinematics(A, W, lane);
-    stage_sync(W);
+    stage_sync(W, 3);
     bool clamped = dynamics(A, W, lane);
-    stage_sync(W);
+    stage_sync(W, 3);
     collide(A, W, lane);
-    stage_sync(W);
+    stage_sync(W, 3);
     make_rows(A, W, lane, C);
-    stage_sync(W, 1);
+    stage_sync(W, 2);
     SubRes r;
     r.niter = solve(A, W, lane, C, a_i);
     r.touch = touch_force(A, W, lane, C);
-    stage_sync(W);
+    stage_sync(W, 3);
     if (do_integrate) integrate(A, W, lane, clamped, time);
     r.a_i = a_i;
     r.time = time;
@@ -1477,7 +1477,7 @@ struct ArmTask {
     for (int k = 0; k < 3; k++) tcp[k] = (double)W.xpos[A.tcp_slot][k] + (double)v[k] + (double)o[k];
   }
 
-  struct Out { double obs[16]; double reward; int terminated, truncated, success, done; };
+  struct Out { double obs[16]; double reward; int terminated, truncated, success, done, nit_sum, nit_max, h4, h8, h16, h32; };
 
   // observation + reward + termination of the CURRENT state (kinematics must be fresh)
   __device__ static void observe(const AM& A, const WM& W, const TS& T, Out& o) {
@@ -1540,14 +1540,21 @@ struct ArmTask {
       if (A.action_dim == 7) servoJ(W, lane, T, action);
       else servoL(A, W, lane, T, action);
     }
+    int nit_sum = 0, nit_max = 0;
+    o.h4 = o.h8 = o.h16 = o.h32 = 0;
     for (int k = 0; k < A.n_sub; k++) {
       before_substep(A, W, lane, T);
       typename E::SubRes so = E::substep(&W, lane, a_i, T.time, 1);
       a_i = so.a_i; T.time = so.time;
+      nit_sum += so.niter; nit_max = so.niter > nit_max ? so.niter : nit_max;
+#ifdef MJS_NIT_HIST
+      o.h4 += so.niter >= 3; o.h8 += so.niter >= 6; o.h16 += so.niter >= 12; o.h32 += so.niter >= 30;
+#endif
       if (A.kind == MJS_TASK_BUTTON) switch_update(A, T, so.touch);
     }
     E::kinematics_only(&W, lane);
     observe(A, W, T, o);
+    o.nit_sum = nit_sum; o.nit_max = nit_max;
     T.ret += o.reward;
     T.len += 1;
     bool bad = false;
@@ -1686,6 +1693,12 @@ __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
   if (lane == 0) {
     if (io.reward) io.reward[e] = (float)o.reward;
     if (io.flags) reinterpret_cast<uchar4*>(io.flags)[e] = make_uchar4(o.terminated, o.truncated, o.success, o.done);
+    if (io.stats) {  // solver effort: env-substeps and Newton iterations (mjs_stats slots 6 and 7)
+      atomicAdd(io.stats + 6, (double)A.n_sub); atomicAdd(io.stats + 7, (double)o.nit_sum);
+#ifdef MJS_NIT_HIST
+      atomicAdd(io.stats + 2, (double)o.h4); atomicAdd(io.stats + 3, (double)o.h8); atomicAdd(io.stats + 4, (double)o.h16); atomicAdd(io.stats + 5, (double)o.h32);
+#endif
+    }
     if (o.done && io.stats) {
       atomicAdd(io.stats + 0, T.ret); atomicAdd(io.stats + 1, (double)T.len); atomicAdd(io.stats + 2, 1.0);
       atomicAdd(io.stats + 3, (double)o.success); atomicAdd(io.stats + 4, (double)o.truncated);

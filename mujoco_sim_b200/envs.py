@@ -129,7 +129,7 @@ class BatchedMujocoSimEnv:
 
     def step_host(self, actions: np.ndarray, obs: np.ndarray, reward: np.ndarray, flags: np.ndarray):
         """End-to-end call with HOST numpy buffers (H2D + step + D2H inside the library)."""
-        _lib.check(self._L.mjs_step_host(self._h, actions.ctypes.data_as(ctypes.c_void_p), obs.ctypes.data_as(ctypes.c_void_p),
+        _lib.check(self._L.mjs_step_host(self._h, actions.ctypes.data_as(ctypes.c_void_p) if actions is not None else None, obs.ctypes.data_as(ctypes.c_void_p),
                                          reward.ctypes.data_as(ctypes.c_void_p), flags.ctypes.data_as(ctypes.c_void_p), None, int(self.autoreset)))
 
     def join_aux(self):
@@ -150,7 +150,7 @@ class BatchedMujocoSimEnv:
     def stats(self, reset: bool = True):
         out = (ctypes.c_double * 8)()
         _lib.check(self._L.mjs_stats(self._h, out, int(reset)))
-        keys = ["return_sum", "length_sum", "episodes", "successes", "truncations", "errors", "env_steps", "_"]
+        keys = ["return_sum", "length_sum", "episodes", "successes", "truncations", "errors", "substeps", "newton_iterations"]
         return dict(zip(keys, list(out)))
 
     def stats_tensor(self) -> torch.Tensor:

@@ -8,7 +8,7 @@ from __future__ import annotations
 import torch
 import torch.distributed as dist
 
-STAT_KEYS = ["return_sum", "length_sum", "episodes", "successes", "truncations", "errors", "env_steps", "_"]
+STAT_KEYS = ["return_sum", "length_sum", "episodes", "successes", "truncations", "errors", "substeps", "newton_iterations"]
 
 
 def env_offset(rank: int, envs_per_gpu: int) -> int:

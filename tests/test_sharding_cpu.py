@@ -40,7 +40,7 @@ def test_two_rank_sharding_and_stats_allreduce():
     assert [r[1] for r in res] == [0, 4096]
     for _, _, tot, rate, ms in res:
         assert tot["return_sum"] == -4.5 and tot["length_sum"] == 300.0 and tot["episodes"] == 4.0 and tot["successes"] == 1.0
-        assert tot["env_steps"] == 2 * 4096 * 10.0
+        assert tot["substeps"] == 2 * 4096 * 10.0
         assert ms == 6.0 and abs(rate - 2 * 4096 * 10 / 6e-3) < 1e-6
 
 
