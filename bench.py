@@ -3,7 +3,7 @@
     python bench.py --gpus N --steps K --warmup W          (N>1: launched by torchrun, one rank per GPU)
     python bench.py --impl reference ...                   (CPU arm: the oracle port on the host cores)
 
-One "step" = one control step (20 physics substeps + task hooks + obs) of every env of the shard.
+One "step" = one control step (n_sub physics substeps + task hooks + obs; Planar Push: 20) of every env of the shard.
 Prints ONE JSON line on rank 0.  See DESIGN.md "Measurement" for how each field is produced.
 """
 from __future__ import annotations
@@ -25,12 +25,13 @@ import numpy as np  # noqa: E402
 
 WORKLOADS = {
     # name -> (task, default envs per GPU, algorithmic flops / env-step, algorithmic bytes / env-step)  
-    "planar_push": ("robot_planar_push", 5328, 0.86e6, 771.0),   # 148 SMs x 12 FP64 warps x 3 waves
+    "planar_push": ("robot_planar_push", 42624, 0.86e6, 771.0),  # 148 SMs x 12 FP64 warps x 24 waves (launch tail amortised)
     "point_mass_reach": ("point_mass_reach", 65536, 3.6e3, 151.0),
     "robot_reach": ("robot_reach", 16384, 0.115e6, 283.0),
     "push_button": ("robot_push_button", 4736, 0.58e6, 539.0),
 }
 METRIC = "env-steps/s (device-timed) Planar Push"
+MIXED_ENVS = 37888  # 148 SMs x 16 FP32 warps x 16 waves
 FP32_PEAK_TFLOPS_FALLBACK = 148 * 128 * 2 * 1.965e9 / 1e12  # SMs x FP32 lanes x FMA x clocks.max.sm = 74.4
 
 
@@ -82,7 +83,7 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------- CPU arm
-def _oracle_worker(bundle, states, actions, steps, tol_scale, out, idx):
+def _oracle_worker(bundle, states, actions, steps, tol_scale, out, idx, burn=0):
     import ctypes
 
     from oracle.oracle import OracleEnvs
@@ -91,13 +92,15 @@ def _oracle_worker(bundle, states, actions, steps, tol_scale, out, idx):
     ora = OracleEnvs(bundle, n)
     ctypes.memmove(ora.states, states, ctypes.sizeof(states))
     ora.tol_scale = tol_scale
+    for k in range(burn):  # untimed: age the scenes to the mean age of the GPU arm's stationary mix
+        ora.step_raw(actions[k % len(actions)])
     t0 = time.perf_counter()
     for k in range(steps):
         ora.step_raw(actions[k])
     out[idx] = time.perf_counter() - t0
 
 
-def cpu_oracle_rate(task: str, envs_per_core: int, steps: int, cores: int | None = None, seed: int = 0):
+def cpu_oracle_rate(task: str, envs_per_core: int, steps: int, cores: int | None = None, seed: int = 0, burn: int = -1):
     """Time the double-precision CPU oracle (oracle/mjs_oracle.cpp, MuJoCo's default solver tolerance)
     on `cores` host threads (ctypes releases the GIL), `envs_per_core` envs each, `steps` control steps
     of the same workload (same scene, same action box, settled initial states)."""
@@ -117,18 +120,19 @@ def cpu_oracle_rate(task: str, envs_per_core: int, steps: int, cores: int | None
         raise SystemExit(f"cpu baseline: no host state generator for {task}")
     rng = np.random.RandomState(seed + 1)
     lo = np.array([t.action_lo[k] for k in range(A)]); hi = np.array([t.action_hi[k] for k in range(A)])
+    if burn < 0:
+        burn = t.max_steps // 2 if task == "robot_planar_push" else 0  # mean scene age of the stationary mix
     threads, out = [], [0.0] * cores
     for c in range(cores):
         chunk = copy_states((type(init[0]) * envs_per_core).from_address(__import__("ctypes").addressof(init) + c * envs_per_core * __import__("ctypes").sizeof(init[0])), envs_per_core)
         acts = rng.uniform(lo, hi, (steps, envs_per_core, A))
-        threads.append(threading.Thread(target=_oracle_worker, args=(bundle, chunk, acts, steps, 1.0, out, c)))
-    t0 = time.perf_counter()
+        threads.append(threading.Thread(target=_oracle_worker, args=(bundle, chunk, acts, steps, 1.0, out, c, burn)))
     for th in threads:
         th.start()
     for th in threads:
         th.join()
-    wall = time.perf_counter() - t0
-    return n * steps / wall, cores, f"{n} envs ({envs_per_core}/thread x {cores} threads) x {steps} control steps, {wall:.1f} s wall"
+    wall = max(out)  # slowest thread's timed loop (all threads run concurrently; the burn-in before it is untimed)
+    return n * steps / wall, cores, f"{n} envs ({envs_per_core}/thread x {cores} threads) x {steps} control steps after {burn} untimed burn-in steps, {wall:.1f} s"
 
 
 # ----------------------------------------------------------------------------- GPU arm
@@ -172,13 +176,17 @@ def run_gpu(args):
     task, n_default, flops_per, bytes_per = WORKLOADS[args.workload]
     N = args.envs or n_default
     if not args.envs and task == "robot_planar_push" and args.precision == "mixed":
-        N = 4736  # 148 SMs x 16 FP32 warps x 2 waves
+        N = MIXED_ENVS
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     env = ms.make(task, N, device=dev, seed=args.seed, env_offset=sharding.env_offset(rank, N), precision=args.precision)
     env.reset()
+    burn_in = args.burn_in
     if task == "robot_planar_push":
         _stagger_episodes(env, env.bundle.task.max_steps, args.seed + rank)
+        if burn_in < 0:
+            burn_in = env.bundle.task.max_steps + 50
+    burn_in = max(burn_in, 0)
     A, O = env.action_dim, env.obs_dim
     lo = torch.tensor([env.bundle.task.action_lo[k] for k in range(A)], device=dev)
     hi = torch.tensor([env.bundle.task.action_hi[k] for k in range(A)], device=dev)
@@ -216,6 +224,11 @@ def run_gpu(args):
             dist.all_reduce(ms_, op=dist.ReduceOp.MAX)
         return float(ms_.item())
 
+    # ---- burn-in (untimed, not part of W): one full episode length, so that every env has gone through its
+    # staggered reset and the population of physical states is stationary (fresh scenes cost ~10 % more per step
+    # than the steady-state mix; a region timed right after reset() would drift)
+    for i in range(burn_in):
+        env.step_flat(actions[i % ring])
     # ---- device-resident arm ("value")
     for i in range(args.warmup):
         env.step_flat(actions[i % ring])
@@ -230,8 +243,8 @@ def run_gpu(args):
         flush.zero_()
     f1.record(stream); torch.cuda.synchronize(dev)
     flush_ms = f0.elapsed_time(f1) / 10
-    # ---- dominant kernel alone: per-launch duration, CUDA events on the launching stream around every launch
-    # (no flush); the median is robust against the low-priority refill kernel co-running on some launches
+    # ---- dominant kernel alone: average per-launch duration, CUDA events on the launching stream around every
+    # launch (no flush; the 2 us job-list kernel that precedes each step kernel is inside the bracket)
     barrier()
     kn = max(5, min(args.steps, 40))
     env.join_aux(); torch.cuda.synchronize(dev)
@@ -242,7 +255,7 @@ def run_gpu(args):
         evs[i + 1].record(stream)
     torch.cuda.synchronize(dev)
     per = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(kn))
-    kernel_ms = per[len(per) // 2]
+    kernel_ms = sum(per) / len(per)
 
     # ---- end-to-end arm: HOST buffers through the C-ABI host call (H2D + step + D2H + sync inside)
     h_act = torch.empty(ring, N, A, dtype=torch.float32).pin_memory()
@@ -268,13 +281,13 @@ def run_gpu(args):
     # Not the headline: it misses the 1e-4 single-step gate on impact steps (tests/test_arm_gpu.py).
     alt = None
     if args.precision == "f64" and not args.no_alt and host_actions:
-        N2 = N if args.envs else 4736
+        N2 = N if args.envs else MIXED_ENVS
         env2 = ms.make(task, N2, device=dev, seed=args.seed, env_offset=rank * N, precision="mixed")
         env2.reset()
         if task == "robot_planar_push":
             _stagger_episodes(env2, env2.bundle.task.max_steps, args.seed + rank)
         act2 = actions[:, :N2].contiguous() if N2 <= N else (lo + (hi - lo) * torch.rand(ring, N2, A, device=dev, generator=g)).float()
-        for i in range(args.warmup):
+        for i in range(burn_in + args.warmup):
             env2.step_flat(act2[i % ring])
         main_env, env = env, env2
         t2 = timed_region(lambda i: env2.step_flat(act2[(args.warmup + i) % ring]), args.steps)
@@ -300,17 +313,17 @@ def run_gpu(args):
             "ms_per_step": t_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 dynamics/solver + f64 state integration" if args.precision == "mixed" else "f64",
             "data": "synthetic (device reset kernel initial states, uniform random actions in the reachable workspace box)",
-            "config": {"workload": (f"{args.workload}: UR5e + cylinder pusher + 3 cylinder props, 20 substeps/step, {N} envs/GPU" if host_actions
+            "config": {"workload": (f"{args.workload}: UR5e + cylinder pusher + 3 cylinder props, {env.bundle.task.n_sub} substeps/step, {N} envs/GPU" if host_actions
                                     else f"{args.workload}: {env.bundle.task.n_sub} substeps/step, {N} envs/GPU, device-drawn actions"),
                        "envs_per_gpu": N, "precision": args.precision, "l2": f"flushed between timed iterations (256 MiB memset inside the region, {flush_ms:.3f} ms each)",
-                       "episodes": "phases staggered over [0,500): steady-state auto-reset rate"},
+                       "episodes": f"phases staggered over [0,max_steps) + {burn_in} untimed burn-in steps: stationary state mix and auto-reset rate"},
             "e2e": {"value": world * N * args.steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": N * A * 4 if host_actions else 0,
                     "d2h_bytes_per_step": N * (O + 1) * 4 + N * 4},
             "gpu_launches": int(launches),
             "clocks": clk.summary(),
             "roofline": {"bound": bound, "achieved": kern_rate * flops_per / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": kern_rate * flops_per / 1e12 / fp32_peak, "traffic": None,
-                         "kernel": "arm_step_kernel", "kernel_ms": kernel_ms, "flops_per_env_step": flops_per,
+                         "kernel": "arm_step_kernel", "kernel_ms": kernel_ms, "kernel_ms_median": per[len(per) // 2], "flops_per_env_step": flops_per,
                          "peak_source": f"148 SMs x {lanes} {bound.upper()} lanes x 2 x clocks.max.sm {sm_max:.0f} MHz, nominal non-tensor FMA peak (MEASURED_PEAKS.json has only HBM and bf16 tensor peaks)",
                          "hbm": {"achieved": kern_rate * bytes_per / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": kern_rate * bytes_per / 1e9 / hbm_peak,
                                  "peak_source": peak_src, "bytes_per_env_step": bytes_per}},
@@ -333,7 +346,7 @@ def run_reference(args):
     task = WORKLOADS[args.workload][0]
     epc = args.cpu_envs_per_core
     for _ in range(1):
-        cpu_oracle_rate(task, epc, max(1, min(args.warmup, 3)))  # warm-up (page-in, thread start)
+        cpu_oracle_rate(task, epc, max(1, min(args.warmup, 3)), burn=0)  # warm-up (page-in, thread start)
     rate, cores, sample = cpu_oracle_rate(task, epc, args.steps)
     n = epc * cores
     return {
@@ -358,10 +371,11 @@ def main():
     ap.add_argument("--envs", type=int, default=0, help="envs per GPU (default: the workload's)")
     ap.add_argument("--precision", default="f64", choices=["mixed", "f64"])
     ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--burn-in", type=int, default=-1, help="untimed steps before warm-up (default: one episode length + 50 for Planar Push, else 0)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-alt", action="store_true", help="skip the secondary precision=mixed measurement")
-    ap.add_argument("--cpu-envs-per-core", type=int, default=32)
-    ap.add_argument("--cpu-steps", type=int, default=60)
+    ap.add_argument("--cpu-envs-per-core", type=int, default=64)
+    ap.add_argument("--cpu-steps", type=int, default=300)
     args = ap.parse_args()
     if args.impl == "reference":
         if args.steps > 200:

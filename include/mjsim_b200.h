@@ -79,6 +79,9 @@ int mjs_debug_forward(MjsSim* sim, int env, double* h_out, int n);
 /* Test hook: continue the current control step of every env by k physics substeps (no before_step
  * hook, no outputs), so tests can split a control step at a substep boundary. */
 int mjs_debug_substeps(MjsSim* sim, int k);
+/* Test/profiling hook: the first call arms per-env timers in the step kernel; later calls copy, per env, the 4 words
+ * {start ns, end of control step ns, end ns, newton_iterations << 32 | max_iterations << 16 | smid} of the last launch. */
+int mjs_debug_times(MjsSim* sim, long long* h_out, int n);
 
 /* Number of kernels this library launched since creation (bench `gpu_launches`). */
 long long mjs_launch_count(const MjsSim* sim);

@@ -336,6 +336,12 @@ int mjs_debug_substeps(MjsSim* s, int k) {
   return arm_debug_substeps(s->arm, k);
 }
 
+int mjs_debug_times(MjsSim* s, long long* h_out, int n) {
+  if (!s->arm) { mjs_set_error("mjs_debug_times: articulated tasks only"); return -1; }
+  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  return arm_debug_times(s->arm, h_out, n);
+}
+
 int mjs_stats_device(MjsSim* s, double** d_out) { *d_out = s->d_stats; return 0; }
 
 int mjs_stats(MjsSim* s, double* h_out8, int reset) {

@@ -32,6 +32,14 @@ ArmSim* arm_create(const MjsModel& m, const MjsTask& t, int N, unsigned long lon
     cudaMemset(a->slot_sd, 0, sizeof(double) * (size_t)a->SD * N);
     cudaMemset(a->slot_si, 0, sizeof(int) * (size_t)a->SI * N);
     cudaMemset(a->slot_ready, 0, sizeof(int) * (size_t)N);
+    // settle jobs in flight ~ N * (settle_steps / n_sub) / episode length (1.2 % of N for Planar Push): room for 3 %
+    // (rounded up to whole blocks at launch); a backlog only delays slots, which are needed an episode later
+    a->job_cap = N * 3 / 100 + 1;
+    if (cudaMalloc(&a->slot_prog, sizeof(int) * (size_t)N) != cudaSuccess || cudaMalloc(&a->jobs, sizeof(int) * ((size_t)a->job_cap + 64 + 2)) != cudaSuccess) {
+      mjs_set_error("arm engine: cudaMalloc (settle jobs) failed"); delete a; return nullptr;
+    }
+    cudaMemset(a->slot_prog, 0, sizeof(int) * (size_t)N);
+    cudaMemset(a->jobs, 0, sizeof(int) * ((size_t)a->job_cap + 64 + 2));
     int lo = 0, hi = 0;
     cudaDeviceGetStreamPriorityRange(&lo, &hi);
     cudaStreamCreateWithPriority(&a->side, cudaStreamNonBlocking, lo);  // lowest priority: fills gaps
@@ -46,10 +54,10 @@ ArmSim* arm_create(const MjsModel& m, const MjsTask& t, int N, unsigned long lon
 void arm_destroy(ArmSim* a) {
   if (!a) return;
   arm_forget_f32(a); arm_forget_f64(a);
-  cudaFree(a->sd); cudaFree(a->si); cudaFree(a->d_debug);
+  cudaFree(a->sd); cudaFree(a->si); cudaFree(a->d_debug); cudaFree(a->d_times);
   if (a->slot_ready) {
     cudaStreamSynchronize(a->side);
-    cudaFree(a->slot_sd); cudaFree(a->slot_si); cudaFree(a->slot_obs); cudaFree(a->slot_ready);
+    cudaFree(a->slot_sd); cudaFree(a->slot_si); cudaFree(a->slot_obs); cudaFree(a->slot_ready); cudaFree(a->slot_prog); cudaFree(a->jobs);
     cudaStreamDestroy(a->side); cudaEventDestroy(a->ev_step); cudaEventDestroy(a->ev_refill);
   }
   delete a;
@@ -60,7 +68,7 @@ static ArmIO make_io(ArmSim* a) {
   memset(&io, 0, sizeof(io));
   { const char* lv = getenv("MJS_SYNC_LEVEL"); io.sync_level = lv ? atoi(lv) : 2; /* 1: barrier at substep start; 2: + before the solve and per Newton iteration; 3: every stage */ }
   io.sd = a->sd; io.si = a->si; io.stats = a->d_stats;
-  io.slot_sd = a->slot_sd; io.slot_si = a->slot_si; io.slot_obs = a->slot_obs; io.slot_ready = a->slot_ready; io.N = a->N; io.seed = a->seed; io.env_offset = a->env_offset;
+  io.slot_sd = a->slot_sd; io.slot_si = a->slot_si; io.slot_obs = a->slot_obs; io.slot_ready = a->slot_ready; io.slot_prog = a->slot_prog; io.times = a->d_times; io.N = a->N; io.seed = a->seed; io.env_offset = a->env_offset;
   return io;
 }
 
@@ -99,10 +107,22 @@ int arm_step(ArmSim* a, const float* d_actions, float* d_obs, float* d_reward, u
   io.actions = d_actions; io.obs = d_obs; io.reward = d_reward; io.flags = d_flags; io.final_obs = d_final_obs;
   io.autoreset = autoreset; io.step_index = step_index;
   if (!autoreset) { io.slot_ready = nullptr; }
-  int r = dispatch(a, 0, io, st);
-  if (r < 0) return r;
-  int q = autoreset ? maybe_refill(a, st) : 0;
-  return q < 0 ? q : r + q;
+  static const bool side_refill = getenv("MJS_SIDE_REFILL") && atoi(getenv("MJS_SIDE_REFILL"));  // A/B: the co-running refill kernel
+  if (io.slot_ready && side_refill) {
+    int r = dispatch(a, 0, io, st);
+    if (r < 0) return r;
+    int q = maybe_refill(a, st);
+    return q < 0 ? q : r + q;
+  }
+  if (io.slot_ready) {
+    // a refill kernel started by mjs_reset must be done before job warps touch the slots
+    if (a->refill_pending) { MJS_CUDA_CHECK(cudaStreamWaitEvent(st, a->ev_refill, 0)); a->refill_pending = 0; }
+    int* counters = a->jobs + a->job_cap + 64;  // the launch rounds job_cap up to whole blocks (< 64 warps)
+    io.jobs = a->jobs; io.job_cap = a->job_cap;
+    io.njobs = counters + (a->step_launches & 1); io.njobs_next = counters + ((a->step_launches + 1) & 1);
+    a->step_launches++;
+  }
+  return dispatch(a, 0, io, st);
 }
 
 // make `st` wait for the refill work in flight (bench: close the timed region)
@@ -161,6 +181,19 @@ int arm_get_state(ArmSim* a, MjsEnvState* h, int first, int count) {
     if (a->nobj == 0) unpack<0>(h[i], sd.data() + (size_t)i * a->SD, si.data() + (size_t)i * a->SI);
     else unpack<3>(h[i], sd.data() + (size_t)i * a->SD, si.data() + (size_t)i * a->SI);
   }
+  return 0;
+}
+
+// first call arms the per-env timers of the step kernel; later calls read them back
+int arm_debug_times(ArmSim* a, long long* h_out, int n) {
+  size_t words = 4 * (size_t)a->N;
+  if (!a->d_times) {
+    MJS_CUDA_CHECK(cudaMalloc(&a->d_times, words * sizeof(long long)));
+    MJS_CUDA_CHECK(cudaMemset(a->d_times, 0, words * sizeof(long long)));
+    return 0;
+  }
+  MJS_CUDA_CHECK(cudaDeviceSynchronize());
+  MJS_CUDA_CHECK(cudaMemcpy(h_out, a->d_times, sizeof(long long) * ((size_t)n < words ? (size_t)n : words), cudaMemcpyDeviceToHost));
   return 0;
 }
 

@@ -13,3 +13,4 @@ int arm_get_state(ArmSim* a, MjsEnvState* h, int first, int count);
 int arm_debug_forward(ArmSim* a, int env, double* h_out, int n);
 int arm_join_aux(ArmSim* a, cudaStream_t st);
 int arm_debug_substeps(ArmSim* a, int k);
+int arm_debug_times(ArmSim* a, long long* h_out, int n);

@@ -1376,6 +1376,13 @@ struct ArmIO {
   int* slot_si;
   float* slot_obs;
   int* slot_ready;
+  // settle jobs folded into the step kernel's grid (arm_jobs_kernel + the job blocks of arm_step_kernel)
+  int* slot_prog;   // settle substeps already done for the slot under preparation (0: not started)
+  int* jobs;        // env ids whose slot is empty or in preparation, rebuilt before every step launch
+  int* njobs;       // number of entries wanted this launch (may exceed job_cap: the rest waits a step)
+  int* njobs_next;  // the other counter of the ping-pong pair, cleared for the next launch
+  int job_cap, job_blocks;
+  long long* times;  // test hook (mjs_debug_times): per env {start, end of control step, end, nit_sum<<32 | nit_max<<16 | smid} in ns
 };
 
 template <typename real, int NOBJ>
@@ -1564,6 +1571,33 @@ struct ArmTask {
 
   // Episode reset: sample boxes, IK, mj_forward, settle (Planar Push)
   __device__ static void reset_env(const AM& A, WM& W, int lane, const ArmIO& io, int e, TS& T, real& a_i, Out& o) {
+    reset_begin(A, W, lane, io, e, T, a_i);
+    // mj_forward at the reset state (actuator force is zero: ctrl == qpos, qvel == 0),
+    // then the settle steps (robot_planar_push.py:160-161).  substep = step1 + step2, so
+    // N settle steps are N substeps; the reference's extra re-solve of the forward pass
+    // restarts from a converged warm start and changes nothing.
+    typename E::SubRes so;
+    if (A.settle_steps > 0) {
+      for (int k = 0; k < A.settle_steps; k++) {
+        so = E::substep(&W, lane, a_i, T.time, 1);
+        a_i = so.a_i; T.time = so.time;
+      }
+      reset_finish(A, W, lane, T, o);
+    } else {
+      so = E::substep(&W, lane, a_i, T.time, 0);
+      a_i = so.a_i;
+      if (A.kind == MJS_TASK_BUTTON) switch_update(A, T, so.touch);
+      observe(A, W, T, o);
+    }
+  }
+  // the observation of a settled reset state (settle_steps > 0)
+  __device__ static void reset_finish(const AM& A, WM& W, int lane, TS& T, Out& o) {
+    E::kinematics_only(&W, lane);
+    if (A.kind == MJS_TASK_BUTTON) switch_update(A, T, (real)0);
+    observe(A, W, T, o);
+  }
+  // sampling half of a reset: spawn pose -> IK, target, props; leaves qpos/qvel/ctrl in W and T zeroed
+  __device__ static void reset_begin(const AM& A, WM& W, int lane, const ArmIO& io, int e, TS& T, real& a_i) {
     unsigned genv = io.env_offset + e;
     T.episode += 1;
     unsigned ep = (unsigned)T.episode;
@@ -1605,24 +1639,6 @@ struct ArmTask {
     a_i = 0;
     init_static(A, W, lane, T);
     __syncwarp();
-    // mj_forward at the reset state (actuator force is zero: ctrl == qpos, qvel == 0),
-    // then the settle steps (robot_planar_push.py:160-161).  substep = step1 + step2, so
-    // N settle steps are N substeps; the reference's extra re-solve of the forward pass
-    // restarts from a converged warm start and changes nothing.
-    typename E::SubRes so;
-    if (A.settle_steps > 0) {
-      for (int k = 0; k < A.settle_steps; k++) {
-        so = E::substep(&W, lane, a_i, T.time, 1);
-        a_i = so.a_i; T.time = so.time;
-      }
-      so.touch = 0;
-      E::kinematics_only(&W, lane);
-    } else {
-      so = E::substep(&W, lane, a_i, T.time, 0);
-      a_i = so.a_i;
-    }
-    if (A.kind == MJS_TASK_BUTTON) switch_update(A, T, so.touch);
-    observe(A, W, T, o);
   }
 };
 
@@ -1643,6 +1659,73 @@ __device__ __forceinline__ void arm_write_out(const ArmModel<real>& A, const Arm
   }
 }
 
+// Settle jobs.  An episode reset of Planar Push costs settle_steps (150) physics substeps -- six control
+// steps' worth -- so the NEXT episode of every env is prepared ahead of time into a slot, n_sub substeps
+// per step launch, by warps of the step kernel's own grid (full blocks that share an SM like any other
+// step block; a co-running kernel of small blocks kept whole SMs away from the step blocks instead).
+// arm_jobs_kernel lists the envs whose slot is empty or in preparation; job warp j takes jobs[j].
+static __global__ void arm_jobs_kernel(ArmIO io) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e == 0) *io.njobs_next = 0;
+  if (e >= io.N) return;
+  if (*((volatile int*)(io.slot_ready + e)) != 0) return;
+  int k = atomicAdd(io.njobs, 1);
+  if (k < io.job_cap) io.jobs[k] = e;
+}
+
+template <typename real, int NOBJ>
+__device__ __noinline__ void arm_settle_job(const ArmModel<real>& A, WarpMem<real, NOBJ>& W, const ArmIO& io, int j, int lane) {
+  using TK = ArmTask<real, NOBJ>;
+  using E = ArmEngine<real, NOBJ>;
+  using L = ArmLayout<NOBJ>;
+  int nj = *io.njobs;
+  if (j >= (nj < io.job_cap ? nj : io.job_cap)) return;
+  int e = io.jobs[j];
+  ArmIO ios = io;
+  ios.sd = io.slot_sd; ios.si = io.slot_si;
+  int prog = io.slot_prog[e];
+  // the env's current episode id; its own warp may be rewriting the record right now, but the id only
+  // changes there on an inline reset, and a slot prepared for the wrong episode is discarded at adoption
+  int episode = *((volatile int*)(io.si + (size_t)e * L::SI + L::I_EPISODE));
+  typename TK::TS T;
+  real a_i;
+  if (prog > 0) {
+    TK::load(A, W, ios, e, lane, T, a_i);
+    if (T.episode != episode + 1) prog = 0;  // overtaken: start again for the right episode
+  }
+  if (prog == 0) {
+    if (lane == 0) { W.status = 0; W.sync = 0; }
+    T.episode = episode; T.swp = 0; T.status = 0;
+    for (int k = 0; k < 3; k++) T.ovr[k] = io.sd[(size_t)e * L::SD + L::OVR + k];  // constant per env outside Button Push
+    TK::reset_begin(A, W, lane, io, e, T, a_i);
+  }
+  int todo = A.settle_steps - prog;
+  if (todo > A.n_sub) todo = A.n_sub;
+  for (int k = 0; k < todo; k++) {
+    typename E::SubRes so = E::substep(&W, lane, a_i, T.time, 1);
+    a_i = so.a_i; T.time = so.time;
+  }
+  prog += todo;
+  bool finished = prog >= A.settle_steps;
+  if (finished) {
+    typename TK::Out o;
+    TK::reset_finish(A, W, lane, T, o);
+    if (lane < 16) {
+      double v = 0;
+#pragma unroll
+      for (int k = 0; k < 16; k++) if (k == lane) v = o.obs[k];
+      io.slot_obs[(size_t)e * 16 + lane] = (float)v;
+    }
+  }
+  T.status = 0;
+  TK::store(W, ios, e, lane, T, a_i);
+  __syncwarp();
+  if (lane == 0) {
+    io.slot_prog[e] = finished ? 0 : prog;
+    if (finished) { __threadfence(); *((volatile int*)(io.slot_ready + e)) = 1; }
+  }
+}
+
 template <typename real, int NOBJ, int WPB, bool SYNC>
 __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
   const ArmModel<real>& A = cmodel<real>();
@@ -1651,15 +1734,21 @@ __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   WM* wm = reinterpret_cast<WM*>(smem_raw);
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int e = blockIdx.x * WPB + warp;
+  WM& W = wm[warp];
+  if ((int)blockIdx.x < io.job_blocks) {  // the first blocks of the grid prepare next-episode slots (no lock-step)
+    arm_settle_job<real, NOBJ>(A, W, io, blockIdx.x * WPB + warp, lane);
+    return;
+  }
+  int e = ((int)blockIdx.x - io.job_blocks) * WPB + warp;
   bool valid = e < io.N;
   if (!valid) {
     if (!SYNC) return;
     e = io.N - 1;  // lock-step mode: surplus warps shadow the last env (barrier counts must match), write nothing
   }
-  WM& W = wm[warp];
   typename TK::TS T;
   real a_i;
+  long long t_start = 0;
+  if (io.times) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
   TK::load(A, W, io, e, lane, T, a_i, SYNC ? io.sync_level : 0);
   // action (all lanes hold the full vector)
   double action[8];
@@ -1681,6 +1770,13 @@ __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
   typename TK::Out o;
   TK::control_step(A, W, lane, T, a_i, action, o);
   if (!valid) return;  // all barriers of this launch are behind us
+  if (io.times && lane == 0) {
+    long long t1; unsigned smid;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    io.times[4 * (size_t)e] = t_start; io.times[4 * (size_t)e + 1] = t1;
+    io.times[4 * (size_t)e + 3] = ((long long)o.nit_sum << 32) | ((long long)(o.nit_max & 0xffff) << 16) | (smid & 0xffff);
+  }
   __syncwarp();
   if (lane == 0) W.sync = 0;  // an inline reset below runs on its own: no further block barriers
   __syncwarp();
@@ -1715,7 +1811,11 @@ __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
       int rdy = 0;
       if (lane == 0) {
         rdy = *((volatile int*)(io.slot_ready + e));
-        if (rdy) { __threadfence(); rdy = (io.slot_si[(size_t)e * L::SI + L::I_EPISODE] == T.episode + 1) ? 1 : 0; }
+        if (rdy) {
+          __threadfence();
+          rdy = (io.slot_si[(size_t)e * L::SI + L::I_EPISODE] == T.episode + 1) ? 1 : 0;
+          if (!rdy) *((volatile int*)(io.slot_ready + e)) = 0;  // stale (an inline reset overtook it): prepare it again
+        }
       }
       rdy = __shfl_sync(FULLMASK, rdy, 0);
       if (rdy) {
@@ -1729,6 +1829,7 @@ __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
         took = true;
       }
     }
+    if (took && io.times && lane == 0) { long long t2; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t2)); io.times[4 * (size_t)e + 2] = t2; }
     if (took) return;
     typename TK::Out o2;
     T.status |= W.status;
@@ -1738,6 +1839,7 @@ __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
     arm_write_out<real, NOBJ>(A, io, e, lane, o, false);
   }
   TK::store(W, io, e, lane, T, a_i);
+  if (io.times && lane == 0) { long long t2; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t2)); io.times[4 * (size_t)e + 2] = t2; }
 }
 
 // refill == 0: reset the masked envs in place (mjs_reset).
@@ -1774,11 +1876,11 @@ __global__ void __launch_bounds__(WPB * 32) arm_reset_kernel(ArmIO io, int refil
       io.slot_obs[(size_t)e * 16 + lane] = (float)v;
     }
     __syncwarp();
-    if (lane == 0) { __threadfence(); *((volatile int*)(io.slot_ready + e)) = 1; }
+    if (lane == 0) { io.slot_prog[e] = 0; __threadfence(); *((volatile int*)(io.slot_ready + e)) = 1; }
   } else {
     arm_write_out<real, NOBJ>(A, io, e, lane, o, false);
     TK::store(W, io, e, lane, T, a_i);
-    if (io.slot_ready && lane == 0) *((volatile int*)(io.slot_ready + e)) = 0;  // a stale slot would repeat this episode
+    if (io.slot_ready && lane == 0) { io.slot_prog[e] = 0; *((volatile int*)(io.slot_ready + e)) = 0; }  // a stale slot would repeat this episode
   }
 }
 

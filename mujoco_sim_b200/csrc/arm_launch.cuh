@@ -32,7 +32,16 @@ static int launch(ArmSim* a, const ArmModel<real>& M, int which, ArmIO io, cudaS
     auto k = arm_step_kernel<real, NOBJ, WPBS, ARM_STEP_SYNC>;
     size_t smem_step = sizeof(WarpMem<real, NOBJ>) * WPBS;
     MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_step));
-    k<<<(n + WPBS - 1) / WPBS, WPBS * 32, smem_step, st>>>(io);
+    // settle jobs ride in the first job_blocks blocks of the same grid (see arm_settle_job)
+    io.job_blocks = 0;
+    if (io.slot_ready && io.jobs) {
+      io.job_blocks = (io.job_cap + WPBS - 1) / WPBS;
+      io.job_cap = io.job_blocks * WPBS;
+      arm_jobs_kernel<<<(n + 255) / 256, 256, 0, st>>>(io);
+    }
+    k<<<(n + WPBS - 1) / WPBS + io.job_blocks, WPBS * 32, smem_step, st>>>(io);
+    MJS_CUDA_CHECK(cudaGetLastError());
+    return io.job_blocks ? 2 : 1;
   } else if (which == 1 && first == 1) {
     // refill (side stream, low priority): ONE warp per block so a refill block's shared memory fits next to
     // a resident step block instead of taking a whole SM away from the step kernel for 150 substeps

@@ -33,6 +33,11 @@ struct ArmSim {
   int* slot_si;
   float* slot_obs;
   int* slot_ready;
+  int* slot_prog;
+  int* jobs;      // job_cap env ids + the two ping-pong counters behind them
+  int job_cap;
+  unsigned int step_launches;
+  long long* d_times;
   cudaStream_t side;
   cudaEvent_t ev_step, ev_refill;
   int refill_pending;
