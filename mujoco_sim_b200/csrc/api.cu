@@ -336,6 +336,25 @@ int mjs_debug_substeps(MjsSim* s, int k) {
   return arm_debug_substeps(s->arm, k);
 }
 
+int mjs_demo_policy(MjsSim* s, double noise, float* d_actions, int* d_ok, void* stream) {
+  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!d_actions) { mjs_set_error("mjs_demo_policy: d_actions is null"); return -1; }
+  if (s->task.kind == MJS_TASK_POINTMASS) {
+    PmIO io = pm_io(s, nullptr, nullptr, nullptr, nullptr, nullptr, 0);
+    int grid = (s->N + 127) / 128;
+    if (s->precision == MJS_PRECISION_F64) pm_policy_kernel<double><<<grid, 128, 0, st>>>(s->pm_pd, io, d_actions, d_ok, noise);
+    else pm_policy_kernel<float><<<grid, 128, 0, st>>>(s->pm_pf, io, d_actions, d_ok, noise);
+    s->launches++;
+  } else {
+    int r = arm_demo_policy(s->arm, noise, s->step_index, d_actions, d_ok, st);
+    if (r < 0) return r;
+    s->launches += r;
+  }
+  MJS_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
 int mjs_debug_times(MjsSim* s, long long* h_out, int n) {
   if (!s->arm) { mjs_set_error("mjs_debug_times: articulated tasks only"); return -1; }
   MJS_CUDA_CHECK(cudaSetDevice(s->device));

@@ -184,6 +184,14 @@ int arm_get_state(ArmSim* a, MjsEnvState* h, int first, int count) {
   return 0;
 }
 
+int arm_demo_policy(ArmSim* a, double noise, unsigned int step_index, float* d_actions, int* d_ok, cudaStream_t st) {
+  if (a->mf.kind == MJS_TASK_PUSH) { mjs_set_error("mjs_demo_policy: Planar Push has no scripted demonstrator (keyboard tele-operation in the reference)"); return -1; }
+  ArmIO io = make_io(a);
+  io.step_index = step_index;
+  a->pol_actions = d_actions; a->pol_ok = d_ok; a->pol_noise = noise;
+  return dispatch(a, 5, io, st);
+}
+
 // first call arms the per-env timers of the step kernel; later calls read them back
 int arm_debug_times(ArmSim* a, long long* h_out, int n) {
   size_t words = 4 * (size_t)a->N;

@@ -14,3 +14,4 @@ int arm_debug_forward(ArmSim* a, int env, double* h_out, int n);
 int arm_join_aux(ArmSim* a, cudaStream_t st);
 int arm_debug_substeps(ArmSim* a, int k);
 int arm_debug_times(ArmSim* a, long long* h_out, int n);
+int arm_demo_policy(ArmSim* a, double noise, unsigned int step_index, float* d_actions, int* d_ok, cudaStream_t st);

@@ -1569,6 +1569,57 @@ struct ArmTask {
     if (__any_sync(FULLMASK, bad)) { T.status |= MJS_STATUS_NAN; o.done = 1; o.truncated = 1; o.terminated = 0; }
   }
 
+  // Scripted demonstrators: robot_reach.py:222-253, robot_push_button.py:231-300.
+  // Kinematics must be fresh.  Returns false when the task has no scripted demonstrator (Planar Push's is a
+  // keyboard tele-operation, robot_planar_push.py:288-308) or the IK of Button Push's joint action fails.
+  __device__ static bool demo_policy(const AM& A, const WM& W, int lane, const TS& T, const ArmIO& io, int e, double noise, double* action) {
+    double tcp[3];
+    tcp_position(A, W, tcp);
+    for (int k = 0; k < 8; k++) action[k] = 0;
+    if (A.kind == MJS_TASK_REACH) {
+      double d[3], m = 0;
+      for (int k = 0; k < 3; k++) {
+        d[k] = T.target[k] - tcp[k];
+        if (noise > 0) {  // np.random.normal(0, noise_level, 3): Box-Muller on the env's Philox stream
+          double u1 = uniform(io, io.env_offset + e, io.step_index, MJS_RNG_POLICY, 2 * k, 0.0, 1.0), u2 = uniform(io, io.env_offset + e, io.step_index, MJS_RNG_POLICY, 2 * k + 1, 0.0, 1.0);
+          d[k] += noise * sqrt(-2.0 * log(fmax(u1, 1e-300))) * cos(6.283185307179586 * u2);
+        }
+        m = fmax(m, fabs(d[k]));
+      }
+      // "move at most 0.5 m/s": the reference only rescales differences above 0.5 m (and then by the control period)
+      if (m > 0.5) for (int k = 0; k < 3; k++) d[k] = d[k] * 0.5 / m * A.control_dt;
+      for (int k = 0; k < 3; k++) action[k] = tcp[k] + d[k];
+      return true;
+    }
+    if (A.kind != MJS_TASK_BUTTON) return false;
+    // switch.get_position (switch.py:86-87, incl. its scalar-offset quirk) == the task's position observable
+    const real* R = W.xmat[A.touch_slot];
+    real tp[3] = {A.touch_pos[0], A.touch_pos[1], A.touch_pos[2]}, v[3];
+    mat_vec(v, R, tp);
+    double quirk = 0.5 * ((double)A.touch_size[0] / 1.01), sw[3], goal[3];
+    for (int k = 0; k < 3; k++) sw[k] = (double)W.xpos[A.touch_slot][k] + (double)v[k] + quirk;
+    double dxy = hypot(tcp[0] - sw[0], tcp[1] - sw[1]);
+    int phase = T.swa ? 3 : ((tcp[2] > sw[2] && dxy < 0.01) ? 2 : 1);
+    if (phase == 1) {  // first up (clear the button), then above it
+      if (tcp[2] < sw[2] + 0.02) { goal[0] = tcp[0]; goal[1] = tcp[1]; } else { goal[0] = sw[0]; goal[1] = sw[1]; }
+      goal[2] = sw[2] + 0.05;
+    } else if (phase == 2) {
+      for (int k = 0; k < 3; k++) goal[k] = sw[k];
+    } else {
+      for (int k = 0; k < 3; k++) goal[k] = A.button_goal[k];
+      if (dxy < 0.05) goal[2] = sw[2] + 0.1;  // do not touch the button again while leaving
+    }
+    double d[3], m = 0, lim = 0.5 * A.control_dt;  // MAX_SPEED 0.5 m/s
+    for (int k = 0; k < 3; k++) { d[k] = goal[k] - tcp[k]; m = fmax(m, fabs(d[k])); }
+    if (m > lim) for (int k = 0; k < 3; k++) d[k] = d[k] * 0.5 / m * A.control_dt;
+    double tgt[3] = {tcp[0] + d[0], tcp[1] + d[1], tcp[2] + d[2]}, seed[6], q[6];
+    for (int i = 0; i < 6; i++) seed[i] = W.qpos[i];
+    bool ok = tcp_to_joints(A, tgt, seed, q, lane);
+    for (int i = 0; i < 6; i++) action[i] = ok ? q[i] : seed[i];
+    action[6] = 0.0;  // "gripper, which is always closed"
+    return ok;
+  }
+
   // Episode reset: sample boxes, IK, mj_forward, settle (Planar Push)
   __device__ static void reset_env(const AM& A, WM& W, int lane, const ArmIO& io, int e, TS& T, real& a_i, Out& o) {
     reset_begin(A, W, lane, io, e, T, a_i);
@@ -1908,6 +1959,34 @@ __global__ void __launch_bounds__(WPB * 32) arm_substeps_kernel(ArmIO io, int k)
     if (A.kind == MJS_TASK_BUTTON) TK::switch_update(A, T, so.touch);
   }
   TK::store(W, io, e, lane, T, a_i);
+}
+
+// mjs_demo_policy: the task's scripted demonstrator evaluated on the current state of every env
+template <typename real, int NOBJ, int WPB>
+__global__ void __launch_bounds__(WPB * 32) arm_policy_kernel(ArmIO io, float* actions, int* ok_out, double noise) {
+  const ArmModel<real>& A = cmodel<real>();
+  using TK = ArmTask<real, NOBJ>;
+  using E = ArmEngine<real, NOBJ>;
+  using WM = WarpMem<real, NOBJ>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WM* wm = reinterpret_cast<WM*>(smem_raw);
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int e = blockIdx.x * WPB + warp;
+  if (e >= io.N) return;
+  WM& W = wm[warp];
+  typename TK::TS T;
+  real a_i;
+  TK::load(A, W, io, e, lane, T, a_i);
+  E::kinematics_only(&W, lane);
+  double action[8];
+  bool ok = TK::demo_policy(A, W, lane, T, io, e, noise, action);
+  if (lane < A.action_dim) {
+    double v = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) if (k == lane) v = action[k];
+    actions[(size_t)e * A.action_dim + lane] = (float)v;
+  }
+  if (ok_out && lane == 0) ok_out[e] = ok ? 1 : 0;
 }
 
 // mj_forward on injected states (mjs_set_state with forward != 0): refresh the warm start

@@ -38,6 +38,7 @@ struct ArmSim {
   int job_cap;
   unsigned int step_launches;
   long long* d_times;
+  float* pol_actions; int* pol_ok; double pol_noise;  // arguments of the pending arm_policy_kernel launch
   cudaStream_t side;
   cudaEvent_t ev_step, ev_refill;
   int refill_pending;
@@ -45,7 +46,7 @@ struct ArmSim {
 };
 
 
-// per-precision launch units: run kernel `which` (0 step, 1 reset/refill, 2 forward, 3 debug, 4 substeps);
+// per-precision launch units: run kernel `which` (0 step, 1 reset/refill, 2 forward, 3 debug, 4 substeps, 5 demo policy);
 // return the number of kernels launched or a negative error
 int arm_launch_f32(ArmSim* a, int which, ArmIO io, cudaStream_t st, int first, int count);
 int arm_launch_f64(ArmSim* a, int which, ArmIO io, cudaStream_t st, int first, int count);

@@ -41,6 +41,7 @@ __host__ __device__ inline double u53(uint32_t a, uint32_t b) {
 #define MJS_RNG_RESET 1u
 #define MJS_RNG_ACTION 2u
 #define MJS_RNG_DISTURB 3u
+#define MJS_RNG_POLICY 4u
 
 // ------------------------------------------------------------------ impedance
 template <typename real>

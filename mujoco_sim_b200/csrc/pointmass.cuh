@@ -196,6 +196,26 @@ __device__ __forceinline__ void pm_forward_reset(const PmParams<real>& P, real q
   pm_solve(P, R, wx, wy);
 }
 
+// Scripted demonstrator of point_reach.py:227-240: step towards the goal, |largest component| = MAX_STEP_SIZE;
+// noise scales each component by 1 + N(0, noise).  One thread per env.
+template <typename real>
+__global__ void __launch_bounds__(128) pm_policy_kernel(PmParams<real> P, PmIO io, float* actions, int* ok_out, double noise) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x, N = io.N;
+  if (e >= N) return;
+  const double* s = io.sd;
+  double a[2] = {s[PM_TX * N + e] - ((double)P.body_x + s[PM_QX * N + e]), s[PM_TY * N + e] - ((double)P.body_y + s[PM_QY * N + e])};
+  if (noise > 0) {
+    Philox4 r = philox4x32_10(io.env_offset + e, io.step_index, MJS_RNG_POLICY, 0, (uint32_t)io.seed, (uint32_t)(io.seed >> 32));
+    double u1 = fmax(u53(r.v[0], r.v[1]), 1e-300), u2 = u53(r.v[2], r.v[3]), rad = sqrt(-2.0 * log(u1));
+    a[0] *= 1.0 + noise * rad * cos(6.283185307179586 * u2);
+    a[1] *= 1.0 + noise * rad * sin(6.283185307179586 * u2);
+  }
+  double m = fmax(fabs(a[0]), fabs(a[1]));
+  double k = m > 0 ? (double)P.action_hi[0] / m : 0.0;  // MAX_STEP_SIZE is the action bound (point_reach.py:208)
+  actions[2 * (size_t)e] = (float)(a[0] * k); actions[2 * (size_t)e + 1] = (float)(a[1] * k);
+  if (ok_out) ok_out[e] = 1;
+}
+
 template <typename real>
 __global__ void __launch_bounds__(128) pm_reset_kernel(PmParams<real> P, PmIO io, const unsigned char* mask) {
   int e = blockIdx.x * blockDim.x + threadIdx.x;

@@ -132,6 +132,16 @@ class BatchedMujocoSimEnv:
         _lib.check(self._L.mjs_step_host(self._h, actions.ctypes.data_as(ctypes.c_void_p) if actions is not None else None, obs.ctypes.data_as(ctypes.c_void_p),
                                          reward.ctypes.data_as(ctypes.c_void_p), flags.ctypes.data_as(ctypes.c_void_p), None, int(self.autoreset)))
 
+    def demonstration_actions(self, noise: float = 0.0):
+        """The task's scripted demonstrator on the current device state (mjs_demo_policy): (actions[N,A] f32, ok[N] bool)."""
+        import torch
+
+        if not hasattr(self, "_pol_a"):
+            self._pol_a = torch.empty(self.num_envs, self.action_dim, dtype=torch.float32, device=self.device)
+            self._pol_ok = torch.empty(self.num_envs, dtype=torch.int32, device=self.device)
+        _lib.check(self._L.mjs_demo_policy(self._h, float(noise), _ptr(self._pol_a), _ptr(self._pol_ok), self._stream()))
+        return self._pol_a, self._pol_ok.bool()
+
     def join_aux(self):
         """Make the current stream wait for background reset preparation in flight."""
         _lib.check(self._L.mjs_join_aux(self._h, self._stream()))

@@ -51,6 +51,7 @@ _SIGS = {
     "mjs_join_aux": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
     "mjs_debug_forward": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.c_int]),
     "mjs_debug_substeps": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "mjs_demo_policy": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
     "mjs_debug_times": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_longlong), ctypes.c_int]),
     "mjs_launch_count": (ctypes.c_longlong, [ctypes.c_void_p]),
     "mjs_num_envs": (ctypes.c_int, [ctypes.c_void_p]),

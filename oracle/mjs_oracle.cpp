@@ -1493,6 +1493,61 @@ void oracle_substeps(const MjsModel* m, const MjsTask* t, MjsEnvState* states, i
   }
 }
 
+// Noise-free scripted demonstrators on the current states: point_reach.py:227-240, robot_reach.py:222-253,
+// robot_push_button.py:231-300.  ok[e] = 0 where the task has none or the IK of the joint action fails.
+void oracle_demo_policy(const MjsModel* m, const MjsTask* t, const MjsEnvState* states, int n, double* actions, int* ok) {
+  static thread_local Data d;
+  for (int e = 0; e < n; e++) {
+    const MjsEnvState* s = states + e;
+    double* a = actions + (size_t)e * t->action_dim;
+    for (int k = 0; k < t->action_dim; k++) a[k] = 0;
+    ok[e] = 1;
+    d.status = 0;
+    kinematics(m, s, &d);
+    if (t->kind == MJS_TASK_POINTMASS) {
+      const double* xp = d.xpos + 3 * t->pm_body;
+      double v[2] = {s->target[0] - xp[0], s->target[1] - xp[1]};
+      double mx = std::max(std::fabs(v[0]), std::fabs(v[1]));
+      double k = mx > 0 ? t->action_hi[0] / mx : 0.0;  // MAX_STEP_SIZE
+      a[0] = v[0] * k; a[1] = v[1] * k;
+      continue;
+    }
+    double tcp[3];
+    tcp_position(m, t, &d, tcp);
+    if (t->kind == MJS_TASK_REACH) {
+      double df[3], mx = 0;
+      for (int k = 0; k < 3; k++) { df[k] = s->target[k] - tcp[k]; mx = std::max(mx, std::fabs(df[k])); }
+      if (mx > 0.5) for (int k = 0; k < 3; k++) df[k] = df[k] * 0.5 / mx * t->control_dt;
+      for (int k = 0; k < 3; k++) a[k] = tcp[k] + df[k];
+    } else if (t->kind == MJS_TASK_BUTTON) {
+      const double* bp = d.site_xpos + 3 * m->touch_site;
+      double quirk = 0.5 * (m->touch_size[0] / 1.01), sw[3], goal[3];
+      for (int k = 0; k < 3; k++) sw[k] = bp[k] + quirk;
+      double dxy = std::hypot(tcp[0] - sw[0], tcp[1] - sw[1]);
+      int phase = s->sw_active ? 3 : ((tcp[2] > sw[2] && dxy < 0.01) ? 2 : 1);
+      if (phase == 1) {
+        if (tcp[2] < sw[2] + 0.02) { goal[0] = tcp[0]; goal[1] = tcp[1]; } else { goal[0] = sw[0]; goal[1] = sw[1]; }
+        goal[2] = sw[2] + 0.05;
+      } else if (phase == 2) {
+        for (int k = 0; k < 3; k++) goal[k] = sw[k];
+      } else {
+        for (int k = 0; k < 3; k++) goal[k] = t->button_goal[k];
+        if (dxy < 0.05) goal[2] = sw[2] + 0.1;
+      }
+      double df[3], mx = 0, lim = 0.5 * t->control_dt;
+      for (int k = 0; k < 3; k++) { df[k] = goal[k] - tcp[k]; mx = std::max(mx, std::fabs(df[k])); }
+      if (mx > lim) for (int k = 0; k < 3; k++) df[k] = df[k] * 0.5 / mx * t->control_dt;
+      double tgt[3] = {tcp[0] + df[0], tcp[1] + df[1], tcp[2] + df[2]}, q[6];
+      bool good = tcp_to_joints(t, tgt, s->qpos + t->arm_qadr, q);
+      for (int i = 0; i < 6; i++) a[i] = good ? q[i] : s->qpos[t->arm_qadr + i];
+      a[6] = 0.0;
+      ok[e] = good ? 1 : 0;
+    } else {
+      ok[e] = 0;  // Planar Push: keyboard tele-operation in the reference
+    }
+  }
+}
+
 int oracle_ncon(const MjsModel* m, const MjsEnvState* s) {
   static thread_local Data d;
   d.status = 0;

@@ -74,6 +74,12 @@ class OracleEnvs:
             ctypes.c_double(self.tol_scale), ctypes.byref(self.flops),
         )
 
+    def demo_policy(self):
+        """noise-free scripted demonstrator actions for the current states: (actions[n, A], ok[n])"""
+        a = np.zeros((self.n, self.task.action_dim)); ok = np.zeros(self.n, np.int32)
+        lib().oracle_demo_policy(ctypes.byref(self.model), ctypes.byref(self.task), self.states, self.n, _dp(a), ok.ctypes.data_as(ctypes.POINTER(ctypes.c_int)))
+        return a, ok.astype(bool)
+
     def finish_reset(self, settle_steps: int = 0):
         lib().oracle_finish_reset(ctypes.byref(self.model), ctypes.byref(self.task), self.states, self.outs, self.n, settle_steps)
         return self.collect()
