@@ -174,12 +174,17 @@ struct ArmEngine {
   // that wait for the slowest member of their group lose less when the group is smaller, at the price of
   // sharing instruction fetches among fewer warps.
   static constexpr int SYNC_GROUP = sizeof(real) == 8 ? ARM_SYNC_GROUP_F64 : ARM_SYNC_GROUP_F32;
+#ifdef ARM_GROUP_SMSP  // experiment: groups follow the warp -> scheduler mapping (warp % 4) instead of warp / SYNC_GROUP
+  __device__ static __forceinline__ int group_id() { return 1 + (((threadIdx.x >> 5) & 3) * ARM_GROUP_SMSP) / 4; }
+#else
+  __device__ static __forceinline__ int group_id() { return 1 + (threadIdx.x >> 5) / SYNC_GROUP; }
+#endif
   __device__ static __forceinline__ void group_sync() {
-    int id = 1 + (threadIdx.x >> 5) / SYNC_GROUP;
+    int id = group_id();
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(SYNC_GROUP * 32) : "memory");
   }
   __device__ static __forceinline__ bool group_or(bool pred) {
-    int id = 1 + (threadIdx.x >> 5) / SYNC_GROUP, r;
+    int id = group_id(), r;
     asm volatile("{ .reg .pred p, q; setp.ne.s32 p, %1, 0; bar.red.or.pred q, %2, %3, p; selp.s32 %0, 1, 0, q; }"
                  : "=r"(r) : "r"((int)pred), "r"(id), "r"(SYNC_GROUP * 32) : "memory");
     return r != 0;
