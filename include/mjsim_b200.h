@@ -84,7 +84,7 @@ int mjs_debug_substeps(MjsSim* sim, int k);
  * Replaces create_demonstration_policy of point_reach.py:227-240, robot_reach.py:222-253 (noise = noise_level) and
  * robot_push_button.py:231-300; Planar Push's demonstrator is keyboard tele-operation and returns an error. */
 int mjs_demo_policy(MjsSim* sim, double noise, float* d_actions, int* d_ok, void* stream);
-/* Test/profiling hook: the first call arms per-env timers in the step kernel; later calls copy, per env, the 4 words
+/* Test/profiling hook: the first call arms per-env timers in the step kernel; later calls copy, per env, 16 words: the 4 words
  * {start ns, end of control step ns, end ns, newton_iterations << 32 | max_iterations << 16 | smid} of the last launch. */
 int mjs_debug_times(MjsSim* sim, long long* h_out, int n);
 

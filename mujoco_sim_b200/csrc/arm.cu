@@ -194,7 +194,7 @@ int arm_demo_policy(ArmSim* a, double noise, unsigned int step_index, float* d_a
 
 // first call arms the per-env timers of the step kernel; later calls read them back
 int arm_debug_times(ArmSim* a, long long* h_out, int n) {
-  size_t words = 4 * (size_t)a->N;
+  size_t words = MJS_TIMES_WORDS * (size_t)a->N;
   if (!a->d_times) {
     MJS_CUDA_CHECK(cudaMalloc(&a->d_times, words * sizeof(long long)));
     MJS_CUDA_CHECK(cudaMemset(a->d_times, 0, words * sizeof(long long)));

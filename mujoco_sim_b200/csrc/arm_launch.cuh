@@ -3,7 +3,8 @@
 #include <cstdlib>
 #include "arm_sim.cuh"
 
-// The kernels read the model from the __constant__ block c_arm_model.  It is
+// The kernels read the model from the __constant__ block c_arm_model (uniform fields) and its global-memory
+// twin g_arm_model (lane-indexed tables).  Both are
 // re-uploaded (after a device sync) whenever a different simulator or precision
 // launches on this device, so several simulators may coexist in a process.
 static const void* g_const_owner[64];
@@ -14,6 +15,7 @@ static int bind_model(const ArmModel<real>& M) {
   if (g_const_owner[dev & 63] == (const void*)&M) return 0;
   MJS_CUDA_CHECK(cudaDeviceSynchronize());
   MJS_CUDA_CHECK(cudaMemcpyToSymbol(c_arm_model, &M, sizeof(M)));
+  MJS_CUDA_CHECK(cudaMemcpyToSymbol(g_arm_model, &M, sizeof(M)));
   g_const_owner[dev & 63] = (const void*)&M;
   return 0;
 }

@@ -13,14 +13,14 @@ dev = torch.device("cuda:0")
 lo = torch.tensor([-0.2, -0.6], device=dev); hi = torch.tensor([0.2, -0.3], device=dev)
 acts = (lo + (hi - lo) * torch.rand(16, N, 2, device=dev)).float().contiguous()
 for i in range(burn): env.step_flat(acts[i % 16])
-buf = (ctypes.c_longlong * (4 * N))()
-env._L.mjs_debug_times(env._h, buf, 4 * N)  # arm
+buf = (ctypes.c_longlong * (16 * N))()
+env._L.mjs_debug_times(env._h, buf, 16 * N)  # arm
 for rep in range(3):
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); env.step_flat(acts[rep]); e1.record(); torch.cuda.synchronize()
-    env._L.mjs_debug_times(env._h, buf, 4 * N)
-    t = np.frombuffer(buf, dtype=np.int64).reshape(N, 4).copy()
+    env._L.mjs_debug_times(env._h, buf, 16 * N)
+    t = np.frombuffer(buf, dtype=np.int64).reshape(N, 16).copy()
     base = t[:, 0].min()
     start, mid, end = (t[:, 0] - base) / 1e6, (t[:, 1] - base) / 1e6, (t[:, 2] - base) / 1e6
     nit = t[:, 3] >> 32; nmax = (t[:, 3] >> 16) & 0xffff; sm = t[:, 3] & 0xffff

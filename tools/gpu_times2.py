@@ -11,13 +11,13 @@ dev = torch.device("cuda:0")
 lo = torch.tensor([-0.2, -0.6], device=dev); hi = torch.tensor([0.2, -0.3], device=dev)
 acts = (lo + (hi - lo) * torch.rand(16, N, 2, device=dev)).float().contiguous()
 for i in range(600): env.step_flat(acts[i % 16])
-buf = (ctypes.c_longlong * (4 * N))()
-env._L.mjs_debug_times(env._h, buf, 4 * N)
+buf = (ctypes.c_longlong * (16 * N))()
+env._L.mjs_debug_times(env._h, buf, 16 * N)
 D, NI = [], []
 for rep in range(6):
     env.step_flat(acts[rep]); torch.cuda.synchronize()
-    env._L.mjs_debug_times(env._h, buf, 4 * N)
-    t = np.frombuffer(buf, dtype=np.int64).reshape(N, 4).copy()
+    env._L.mjs_debug_times(env._h, buf, 16 * N)
+    t = np.frombuffer(buf, dtype=np.int64).reshape(N, 16).copy()
     D.append((t[:, 1] - t[:, 0]) / 1e6); NI.append(t[:, 3] >> 32)
 D = np.array(D); NI = np.array(NI)
 print("own-cost per env-step (ms): mean %.3f p10 %.3f p50 %.3f p90 %.3f p99 %.3f max %.3f" % (D.mean(), np.percentile(D, 10), np.median(D), np.percentile(D, 90), np.percentile(D, 99), D.max()))
