@@ -417,7 +417,7 @@ struct ArmEngine {
       W.fsm[lane] = (real)frc - tau;
     } else if (lane < NV) {
       int k = (lane - ARM_NLINK) / 6, d = (lane - ARM_NLINK) % 6;
-      if (d < 3) W.fsm[lane] = GM().obj_mass[k] * A.gravity[d];
+      if (d < 3) W.fsm[lane] = GM().obj_mass[k] * GM().gravity[d];
       else {
         int b = ARM_NLINK + 6 * k + 3;
         real w[3] = {(real)W.qvel[b], (real)W.qvel[b + 1], (real)W.qvel[b + 2]};
