@@ -24,6 +24,7 @@ ArmSim* arm_create(const MjsModel& m, const MjsTask& t, int N, unsigned long lon
     mjs_set_error("arm engine: cudaMalloc failed"); delete a; return nullptr;
   }
   cudaMalloc(&a->d_debug, sizeof(double) * 1024);
+  if (cudaMalloc(&a->queue, 64) != cudaSuccess) { mjs_set_error("arm engine: cudaMalloc (work queue) failed"); delete a; return nullptr; }
   if (a->mf.settle_steps > 0) {
     if (cudaMalloc(&a->slot_sd, sizeof(double) * (size_t)a->SD * N) != cudaSuccess || cudaMalloc(&a->slot_si, sizeof(int) * (size_t)a->SI * N) != cudaSuccess ||
         cudaMalloc(&a->slot_obs, sizeof(float) * 16 * (size_t)N) != cudaSuccess || cudaMalloc(&a->slot_ready, sizeof(int) * (size_t)N) != cudaSuccess) {
@@ -54,7 +55,7 @@ ArmSim* arm_create(const MjsModel& m, const MjsTask& t, int N, unsigned long lon
 void arm_destroy(ArmSim* a) {
   if (!a) return;
   arm_forget_f32(a); arm_forget_f64(a);
-  cudaFree(a->sd); cudaFree(a->si); cudaFree(a->d_debug); cudaFree(a->d_times);
+  cudaFree(a->sd); cudaFree(a->si); cudaFree(a->d_debug); cudaFree(a->d_times); cudaFree(a->queue);
   if (a->slot_ready) {
     cudaStreamSynchronize(a->side);
     cudaFree(a->slot_sd); cudaFree(a->slot_si); cudaFree(a->slot_obs); cudaFree(a->slot_ready); cudaFree(a->slot_prog); cudaFree(a->jobs);
@@ -121,6 +122,14 @@ int arm_step(ArmSim* a, const float* d_actions, float* d_obs, float* d_reward, u
     io.jobs = a->jobs; io.job_cap = a->job_cap;
     io.njobs = counters + (a->step_launches & 1); io.njobs_next = counters + ((a->step_launches + 1) & 1);
     a->step_launches++;
+  }
+  // Work distribution of the step kernel: MJS_QUEUE=1 -> persistent grid, warps pull envs from an atomic counter
+  // (no lock-step: sync_level 0); MJS_QUEUE=0 -> one block per 12/16 envs with lock-step stage barriers.
+  static const int use_queue = getenv("MJS_QUEUE") ? atoi(getenv("MJS_QUEUE")) : MJS_QUEUE_DEFAULT;
+  if (use_queue) {
+    io.sync_level = 0;
+    io.queue = a->queue;
+    MJS_CUDA_CHECK(cudaMemsetAsync(a->queue, 0, sizeof(int), st));
   }
   return dispatch(a, 0, io, st);
 }

@@ -45,6 +45,11 @@ __device__ __align__(16) unsigned char g_arm_model[sizeof(ArmModel<double>)];
 #define GM() (*reinterpret_cast<const ArmModel<real>*>(g_arm_model))
 #endif
 
+#ifdef MJS_STAGE_CLOCKS_REPEAT
+#define MJS_NCLK 14  // + second (instruction-cache-hot) runs of dynamics and collision
+#else
+#define MJS_NCLK 12
+#endif
 template <typename real, int NOBJ>
 struct WarpMem {
   static constexpr int NV = ARM_NLINK + 6 * NOBJ;
@@ -78,7 +83,7 @@ struct WarpMem {
   int coup;     // bit b: the arm block shares a contact with prop b
   int objcoup;  // non-zero: two props share a contact (dense factorisation path)
 #ifdef MJS_STAGE_CLOCKS
-  long long clk[12];  // profiling build: cycles per stage, accumulated by lane 0
+  long long clk[MJS_NCLK];  // profiling build: cycles per stage, accumulated by lane 0
 #endif
 };
 
@@ -180,10 +185,14 @@ struct ArmEngine {
   // Unroll factor of the outer loops whose bodies index no register array (chain walk, scan steps, contact sides).
   // Rolled: measured +3 % on Planar Push and +6 % on Button Push in f64 against full unrolling (less straight-line code
   // to fetch, same schedule).  Rolling the Cholesky column loops as well measured 4 % (f64) to 19 % (FP32) slower.
+#ifndef ARM_CHOL_UNROLL
+#define ARM_CHOL_UNROLL 6
+#endif
 #ifndef ARM_ROLL_FACTOR
 #define ARM_ROLL_FACTOR 1
 #endif
   static constexpr int ROLL = ARM_ROLL_FACTOR;
+  static constexpr int CHOLU = ARM_CHOL_UNROLL;  // unroll factor of the 6-step column loops of the block Cholesky (6 = straight-line code)
 
   // solver ordering: props first, arm last (no fill-in between props)
   __device__ static __forceinline__ int sidx(int dof) { return dof >= ARM_NLINK ? dof - ARM_NLINK : dof + 6 * NOBJ; }
@@ -678,7 +687,7 @@ struct ArmEngine {
         W.cJ[j][c] = sgn;  // side 0, row 0, column j
         W.cblk[0][c] = 0; W.ccols[0][c] = ARM_NLINK; W.cblk[1][c] = -1; W.ccols[1][c] = 0;
         u[0] = sgn * W.qv[j];
-        mjs_kb<real>(GM().jnt_solref[j], GM().jnt_solimp[j], A.timestep, &kk, &bb);
+        kk = GM().jnt_kb[j][0]; bb = GM().jnt_kb[j][1];
         incl = GM().jnt_margin[j];
         imp = mjs_impedance<real>(GM().jnt_solimp[j], dist, incl);
         diag0 = GM().jnt_diag[j];
@@ -746,7 +755,7 @@ struct ArmEngine {
           W.cblk[side][c] = blk; W.ccols[side][c] = cols;
         }
         C.mu[0] = GM().pair_mu[p][0]; C.mu[1] = GM().pair_mu[p][0]; C.mu[2] = GM().pair_mu[p][1];
-        mjs_kb<real>(GM().pair_solref[p], GM().pair_solimp[p], A.timestep, &kk, &bb);
+        kk = GM().pair_kb[p][0]; bb = GM().pair_kb[p][1];
         incl = GM().pair_incl[p];
         imp = mjs_impedance<real>(GM().pair_solimp[p], dist, incl);
         diag0 = dim == 1 ? GM().pair_tran[p] : GM().pair_tran[p] * (1 + C.mu[0] * C.mu[0]);
@@ -853,104 +862,120 @@ struct ArmEngine {
   // ---- Newton direction, block-sparse path.  Solver order: props first, arm last.
   // Without prop-prop contacts the Hessian is block-arrow: the prop blocks are
   // factorised in parallel (6 column steps for all props at once), then the arm
-  // rows against the coupled props, then the 6x6 arm Schur complement.
+  // rows against the coupled props, then the 6x6 arm Schur complement.  When the
+  // arm shares no contact with a prop either (coup == 0, the common case) the
+  // Hessian is block-diagonal and the arm block rides in the same 6 column steps
+  // and the same 6 + 6 substitution steps as the props: half the serial chain.
+#ifdef MJS_SHARED_CHOL
+  // one copy, called by the Newton loop and by the integrator (second call runs hot in the instruction cache)
+  __device__ static __noinline__ real block_direction(WM& W, int lane, real b) {
+#else
   __device__ static __forceinline__ real block_direction(WM& W, int lane, real b) {
+#endif
     const bool isarm = lane < ARM_NLINK, isobj = lane >= ARM_NLINK && lane < NV;
     const int myc = isarm ? lane : (lane - ARM_NLINK) % 6;
     const int base = isarm ? 6 * NOBJ : ((lane - ARM_NLINK) / 6) * 6;
     const int si = base + myc;
     const int coup = W.coup;
+    const bool indep = coup == 0;                   // warp-uniform
+    const bool isblk = isobj || (isarm && indep);   // lanes of the parallel diagonal-block pass
+    const int lane0 = isarm ? 0 : ARM_NLINK + base; // lane that owns column 0 of this lane's block
     real rdiag = 1;
-    // prop diagonal blocks
-#pragma unroll
+    // diagonal blocks (props, and the arm when it is uncoupled)
+#pragma unroll CHOLU
     for (int c = 0; c < 6; c++) {
       real s = 0;
-      if (isobj && myc >= c) {
+      if (isblk && myc >= c) {
         s = W.H[si][base + c];
         for (int j = 0; j < c; j++) s -= W.H[si][base + j] * W.H[base + c][base + j];
       }
-      real dk = shfl(s, isobj ? ARM_NLINK + base + c : lane);
+      real dk = shfl(s, isblk ? lane0 + c : lane);
       real rd = rsqrt_r<real>(dk);
-      if (isobj) {
+      if (isblk) {
         if (myc == c) { W.H[si][si] = dk * rd; rdiag = rd; }
         else if (myc > c) W.H[si][base + c] = s * rd;
       }
       __syncwarp();
     }
-    // arm rows x coupled prop columns
-    for (int ob = 0; ob < NOBJ; ob++) {
-      if (!((coup >> ob) & 1)) continue;
-#pragma unroll
-      for (int c = 0; c < 6; c++) {
-        int k = 6 * ob + c;
-        real rdk = shfl(rdiag, ARM_NLINK + k);
-        if (isarm) {
-          real s = W.H[si][k];
-          for (int j = 0; j < c; j++) s -= W.H[si][6 * ob + j] * W.H[k][6 * ob + j];
-          W.H[si][k] = s * rdk;
+    if (!indep) {
+      // arm rows x coupled prop columns
+      for (int ob = 0; ob < NOBJ; ob++) {
+        if (!((coup >> ob) & 1)) continue;
+#pragma unroll CHOLU
+        for (int c = 0; c < 6; c++) {
+          int k = 6 * ob + c;
+          real rdk = shfl(rdiag, ARM_NLINK + k);
+          if (isarm) {
+            real s = W.H[si][k];
+            for (int j = 0; j < c; j++) s -= W.H[si][6 * ob + j] * W.H[k][6 * ob + j];
+            W.H[si][k] = s * rdk;
+          }
         }
       }
-    }
-    __syncwarp();
-    // arm Schur complement block
+      __syncwarp();
+      // arm Schur complement block
+#pragma unroll CHOLU
+      for (int c = 0; c < 6; c++) {
+        int k = 6 * NOBJ + c;
+        real s = 0;
+        if (isarm && myc >= c) {
+          s = W.H[si][k];
+          for (int ob = 0; ob < NOBJ; ob++) {
+            if (!((coup >> ob) & 1)) continue;
 #pragma unroll
+            for (int j = 0; j < 6; j++) s -= W.H[si][6 * ob + j] * W.H[k][6 * ob + j];
+          }
+          for (int j = 0; j < c; j++) s -= W.H[si][6 * NOBJ + j] * W.H[k][6 * NOBJ + j];
+        }
+        real dk = shfl(s, c);
+        real rd = rsqrt_r<real>(dk);
+        if (isarm) {
+          if (myc == c) { W.H[si][si] = dk * rd; rdiag = rd; }
+          else if (myc > c) W.H[si][k] = s * rd;
+        }
+        __syncwarp();
+      }
+    }
+    // forward substitution: diagonal blocks in parallel, then the coupled arm
+#pragma unroll CHOLU
     for (int c = 0; c < 6; c++) {
-      int k = 6 * NOBJ + c;
-      real s = 0;
-      if (isarm && myc >= c) {
-        s = W.H[si][k];
+      real yk = shfl(b * rdiag, isblk ? lane0 + c : lane);
+      if (isblk) { if (myc == c) b = yk; else if (myc > c) b -= W.H[si][base + c] * yk; }
+    }
+    if (!indep) {
+      if (isobj) W.dir[lane] = b;
+      __syncwarp();
+      if (isarm) {
         for (int ob = 0; ob < NOBJ; ob++) {
           if (!((coup >> ob) & 1)) continue;
 #pragma unroll
-          for (int j = 0; j < 6; j++) s -= W.H[si][6 * ob + j] * W.H[k][6 * ob + j];
+          for (int j = 0; j < 6; j++) b -= W.H[si][6 * ob + j] * W.dir[ARM_NLINK + 6 * ob + j];
         }
-        for (int j = 0; j < c; j++) s -= W.H[si][6 * NOBJ + j] * W.H[k][6 * NOBJ + j];
       }
-      real dk = shfl(s, c);
-      real rd = rsqrt_r<real>(dk);
-      if (isarm) {
-        if (myc == c) { W.H[si][si] = dk * rd; rdiag = rd; }
-        else if (myc > c) W.H[si][k] = s * rd;
+#pragma unroll CHOLU
+      for (int c = 0; c < 6; c++) {
+        real yk = shfl(b * rdiag, c);
+        if (isarm) { if (myc == c) b = yk; else if (myc > c) b -= W.H[si][6 * NOBJ + c] * yk; }
+      }
+      // backward substitution: arm, then props
+#pragma unroll CHOLU
+      for (int c = 5; c >= 0; c--) {
+        real xk = shfl(b * rdiag, c);
+        if (isarm) { if (myc == c) b = xk; else if (myc < c) b -= W.H[6 * NOBJ + c][si] * xk; }
       }
       __syncwarp();
-    }
-    // forward substitution: props in parallel, then arm
+      if (isarm) W.dir[lane] = b;
+      __syncwarp();
+      if (isobj && ((coup >> (base / 6)) & 1)) {
 #pragma unroll
-    for (int c = 0; c < 6; c++) {
-      real yk = shfl(b * rdiag, isobj ? ARM_NLINK + base + c : lane);
-      if (isobj) { if (myc == c) b = yk; else if (myc > c) b -= W.H[si][base + c] * yk; }
-    }
-    if (isobj) W.dir[lane] = b;
-    __syncwarp();
-    if (isarm) {
-      for (int ob = 0; ob < NOBJ; ob++) {
-        if (!((coup >> ob) & 1)) continue;
-#pragma unroll
-        for (int j = 0; j < 6; j++) b -= W.H[si][6 * ob + j] * W.dir[ARM_NLINK + 6 * ob + j];
+        for (int i = 0; i < 6; i++) b -= W.H[6 * NOBJ + i][si] * W.dir[i];
       }
     }
-#pragma unroll
-    for (int c = 0; c < 6; c++) {
-      real yk = shfl(b * rdiag, c);
-      if (isarm) { if (myc == c) b = yk; else if (myc > c) b -= W.H[si][6 * NOBJ + c] * yk; }
-    }
-    // backward substitution: arm, then props
-#pragma unroll
+    // backward substitution of the parallel blocks
+#pragma unroll CHOLU
     for (int c = 5; c >= 0; c--) {
-      real xk = shfl(b * rdiag, c);
-      if (isarm) { if (myc == c) b = xk; else if (myc < c) b -= W.H[6 * NOBJ + c][si] * xk; }
-    }
-    __syncwarp();
-    if (isarm) W.dir[lane] = b;
-    __syncwarp();
-    if (isobj && ((coup >> (base / 6)) & 1)) {
-#pragma unroll
-      for (int i = 0; i < 6; i++) b -= W.H[6 * NOBJ + i][si] * W.dir[i];
-    }
-#pragma unroll
-    for (int c = 5; c >= 0; c--) {
-      real xk = shfl(b * rdiag, isobj ? ARM_NLINK + base + c : lane);
-      if (isobj) { if (myc == c) b = xk; else if (myc < c) b -= W.H[base + c][si] * xk; }
+      real xk = shfl(b * rdiag, isblk ? lane0 + c : lane);
+      if (isblk) { if (myc == c) b = xk; else if (myc < c) b -= W.H[base + c][si] * xk; }
     }
     return (isarm || isobj) ? b : (real)0;
   }
@@ -1144,8 +1169,9 @@ struct ArmEngine {
       }
       STAGE_CLK(W, 7, tclk);
     }
-    // final forces -> qfrc_constraint
-    contact_eval(W, lane, C, true);
+    // final forces -> qfrc_constraint.  A converged warp evaluated them at its last
+    // iterate already (cf is current); only an exit at max_iter leaves a newer iterate.
+    if (!done) contact_eval(W, lane, C, true);
     __syncwarp();
     if (isdof) W.fcon[lane] = jt_force(W, myblk, d);
     __syncwarp();
@@ -1180,6 +1206,28 @@ struct ArmEngine {
   __device__ static void integrate(const AM& A, WM& W, int lane, bool clamped, double& time) {
     const real h = A.timestep;
     real qacc = 0;
+#ifdef MJS_SHARED_CHOL
+    // The integrator's system is block-diagonal (arm: M + h kv; props: their constant inertia): write it into the
+    // (now free) Hessian scratch in solver order and reuse the Newton direction routine with no coupling.
+    if (lane < NV) {
+      const bool isarm = lane < ARM_NLINK;
+      const int myc = isarm ? lane : (lane - ARM_NLINK) % 6;
+      const int base = isarm ? 6 * NOBJ : ((lane - ARM_NLINK) / 6) * 6;
+      if (isarm) {
+        real dv = (A.integrator == MJS_INT_IMPLICITFAST && !clamped) ? (real)GM().kv[lane] : (real)0;
+#pragma unroll
+        for (int j = 0; j < ARM_NLINK; j++) W.H[base + myc][base + j] = W.Marm[lane][j] + (j == lane ? h * dv : (real)0);
+      } else {
+        int k = (lane - ARM_NLINK) / 6;
+        real md = myc < 3 ? GM().obj_mass[k] : GM().obj_I[k][myc - 3];
+#pragma unroll
+        for (int j = 0; j < 6; j++) W.H[base + myc][base + j] = j == myc ? md : (real)0;
+      }
+    }
+    if (lane == 0) W.coup = 0;
+    __syncwarp();
+    qacc = block_direction(W, lane, lane < NV ? W.fsm[lane] + W.fcon[lane] : (real)0);
+#else
     if (lane < ARM_NLINK) {
       real dv = (A.integrator == MJS_INT_IMPLICITFAST && !clamped) ? (real)GM().kv[lane] : (real)0;
       // 6x6 system in the (now free) Hessian scratch, lanes 0..5 = rows
@@ -1219,6 +1267,7 @@ struct ArmEngine {
       int k = (lane - ARM_NLINK) / 6, d = (lane - ARM_NLINK) % 6;
       qacc = b / (d < 3 ? GM().obj_mass[k] : GM().obj_I[k][d - 3]);
     }
+#endif
     // mj_advance in double
     if (lane < NV) W.qvel[lane] += (double)h * (double)qacc;
     __syncwarp();
@@ -1271,11 +1320,22 @@ struct ArmEngine {
     STAGE_CLK(W, 0, tclk);
 #endif
     stage_sync(W, 3);
+#ifdef MJS_STAGE_CLOCKS_REPEAT
+    bool clamped = dynamics_only(&W, lane);
+    STAGE_CLK(W, 1, tclk);
+    clamped = dynamics_only(&W, lane);
+    STAGE_CLK(W, 12, tclk);
+    collide_only(&W, lane);
+    STAGE_CLK(W, 2, tclk);
+    collide_only(&W, lane);
+    STAGE_CLK(W, 13, tclk);
+#else
     bool clamped = dynamics(A, W, lane);
     STAGE_CLK(W, 1, tclk);
     stage_sync(W, 3);
     collide(A, W, lane);
     STAGE_CLK(W, 2, tclk);
+#endif
     stage_sync(W, 3);
     make_rows(A, W, lane, C);
     STAGE_CLK(W, 3, tclk);
@@ -1292,6 +1352,8 @@ struct ArmEngine {
     return r;
   }
   __device__ static __noinline__ void kinematics_only(WM* Wp, int lane) { kinematics(cmodel<real>(), *Wp, lane); }
+  __device__ static __noinline__ bool dynamics_only(WM* Wp, int lane) { return dynamics(cmodel<real>(), *Wp, lane); }
+  __device__ static __noinline__ void collide_only(WM* Wp, int lane) { collide(cmodel<real>(), *Wp, lane); }
 };
 
 // ===================================================================== analytic UR IK
@@ -1405,7 +1467,7 @@ struct ArmLayout {
   static constexpr int I_STEP = 0, I_TRAJ = 1, I_SWA = 2, I_SWP = 3, I_SWC = 4, I_STATUS = 5, I_EPISODE = 6, I_LEN = 7, SI = 8;
 };
 
-#define MJS_TIMES_WORDS 16  // per-env words of the mjs_debug_times buffer (4 used; 4..15 = stage cycles of a -DMJS_STAGE_CLOCKS build)
+#define MJS_TIMES_WORDS (4 + MJS_NCLK)  // 16; per-env words of the mjs_debug_times buffer (4 used; 4..15 = stage cycles of a -DMJS_STAGE_CLOCKS build)
 struct ArmIO {
   double* sd;
   int* si;
@@ -1431,6 +1493,7 @@ struct ArmIO {
   int* njobs;       // number of entries wanted this launch (may exceed job_cap: the rest waits a step)
   int* njobs_next;  // the other counter of the ping-pong pair, cleared for the next launch
   int job_cap, job_blocks;
+  int* queue;       // non-null: persistent step grid, warps pull work items from this counter (zeroed before the launch)
   long long* times;  // test hook (mjs_debug_times): per env {start, end of control step, end, nit_sum<<32 | nit_max<<16 | smid} in ns
 };
 
@@ -1466,7 +1529,7 @@ struct ArmTask {
     T.status = si[L::I_STATUS]; T.episode = si[L::I_EPISODE]; T.len = si[L::I_LEN];
     if (lane == 0) { W.status = 0; W.sync = sync; }
 #ifdef MJS_STAGE_CLOCKS
-    if (lane < 12) W.clk[lane] = 0;
+    if (lane < MJS_NCLK) W.clk[lane] = 0;
 #endif
     init_static(A, W, lane, T);
     __syncwarp();
@@ -1829,25 +1892,11 @@ __device__ __noinline__ void arm_settle_job(const ArmModel<real>& A, WarpMem<rea
   }
 }
 
-template <typename real, int NOBJ, int WPB, bool SYNC>
-__global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
-  const ArmModel<real>& A = cmodel<real>();
+// One control step of env e by the calling warp (valid == false: a surplus warp of a lock-step block
+// shadowing the last env so that barrier counts match; it writes nothing).
+template <typename real, int NOBJ, bool SYNC>
+__device__ __noinline__ void arm_step_env(const ArmModel<real>& A, WarpMem<real, NOBJ>& W, const ArmIO& io, int e, bool valid, int lane) {
   using TK = ArmTask<real, NOBJ>;
-  using WM = WarpMem<real, NOBJ>;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  WM* wm = reinterpret_cast<WM*>(smem_raw);
-  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  WM& W = wm[warp];
-  if ((int)blockIdx.x < io.job_blocks) {  // the first blocks of the grid prepare next-episode slots (no lock-step)
-    arm_settle_job<real, NOBJ>(A, W, io, blockIdx.x * WPB + warp, lane);
-    return;
-  }
-  int e = ((int)blockIdx.x - io.job_blocks) * WPB + warp;
-  bool valid = e < io.N;
-  if (!valid) {
-    if (!SYNC) return;
-    e = io.N - 1;  // lock-step mode: surplus warps shadow the last env (barrier counts must match), write nothing
-  }
   typename TK::TS T;
   real a_i;
   long long t_start = 0;
@@ -1878,7 +1927,7 @@ __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
     asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
 #ifdef MJS_STAGE_CLOCKS
-    for (int k = 0; k < 12; k++) io.times[MJS_TIMES_WORDS * (size_t)e + 4 + k] = W.clk[k];
+    for (int k = 0; k < MJS_NCLK; k++) io.times[MJS_TIMES_WORDS * (size_t)e + 4 + k] = W.clk[k];
 #endif
     io.times[MJS_TIMES_WORDS * (size_t)e] = t_start; io.times[MJS_TIMES_WORDS * (size_t)e + 1] = t1;
     io.times[MJS_TIMES_WORDS * (size_t)e + 3] = ((long long)o.nit_sum << 32) | ((long long)(o.nit_max & 0xffff) << 16) | (smid & 0xffff);
@@ -1946,6 +1995,45 @@ __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
   }
   TK::store(W, io, e, lane, T, a_i);
   if (io.times && lane == 0) { long long t2; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t2)); io.times[MJS_TIMES_WORDS * (size_t)e + 2] = t2; }
+}
+
+// Work items of one launch: job_blocks * WPB settle jobs first, then the N envs.
+//  * static mode (io.queue == nullptr): block b / warp w owns item b * WPB + w; the warps of a block may run the
+//    substep stages in lock-step (io.sync_level > 0).
+//  * queue mode (io.queue != nullptr, sync_level 0): a persistent grid of one block per SM whose warps each pull the
+//    next item from an atomic counter until the items run out.  A warp never waits for the slowest env of its
+//    block, and the launch has no wave quantisation: its tail is one env-step instead of one block-wave.
+template <typename real, int NOBJ, int WPB, bool SYNC>
+__global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
+  const ArmModel<real>& A = cmodel<real>();
+  using WM = WarpMem<real, NOBJ>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WM* wm = reinterpret_cast<WM*>(smem_raw);
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  WM& W = wm[warp];
+  if (io.queue) {
+    const int njob = io.job_blocks * WPB, total = njob + io.N;
+    for (;;) {
+      int item = 0;
+      if (lane == 0) item = atomicAdd(io.queue, 1);
+      item = __shfl_sync(FULLMASK, item, 0);
+      if (item >= total) return;
+      if (item < njob) arm_settle_job<real, NOBJ>(A, W, io, item, lane);
+      else arm_step_env<real, NOBJ, SYNC>(A, W, io, item - njob, true, lane);  // the host passes sync_level 0 with a queue
+      __syncwarp();
+    }
+  }
+  if ((int)blockIdx.x < io.job_blocks) {  // the first blocks of the grid prepare next-episode slots (no lock-step)
+    arm_settle_job<real, NOBJ>(A, W, io, blockIdx.x * WPB + warp, lane);
+    return;
+  }
+  int e = ((int)blockIdx.x - io.job_blocks) * WPB + warp;
+  bool valid = e < io.N;
+  if (!valid) {
+    if (!SYNC) return;
+    e = io.N - 1;  // lock-step mode: surplus warps shadow the last env (barrier counts must match), write nothing
+  }
+  arm_step_env<real, NOBJ, SYNC>(A, W, io, e, valid, lane);
 }
 
 // refill == 0: reset the masked envs in place (mjs_reset).

@@ -41,7 +41,19 @@ static int launch(ArmSim* a, const ArmModel<real>& M, int which, ArmIO io, cudaS
       io.job_cap = io.job_blocks * WPBS;
       arm_jobs_kernel<<<(n + 255) / 256, 256, 0, st>>>(io);
     }
-    k<<<(n + WPBS - 1) / WPBS + io.job_blocks, WPBS * 32, smem_step, st>>>(io);
+    int blocks = (n + WPBS - 1) / WPBS + io.job_blocks;
+    if (io.queue) {  // persistent grid: as many blocks as are resident at once (one per SM: shared memory is full)
+      static int resident = 0;
+      if (!resident) {
+        int dev = 0, sms = 0, per_sm = 0;
+        MJS_CUDA_CHECK(cudaGetDevice(&dev));
+        MJS_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        MJS_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, WPBS * 32, smem_step));
+        resident = sms * (per_sm > 0 ? per_sm : 1);
+      }
+      if (blocks > resident) blocks = resident;
+    }
+    k<<<blocks, WPBS * 32, smem_step, st>>>(io);
     MJS_CUDA_CHECK(cudaGetLastError());
     return io.job_blocks ? 2 : 1;
   } else if (which == 1 && first == 1) {

@@ -42,6 +42,7 @@ struct ArmModel {
   int ctrllimited[ARM_NLINK], forcelimited[ARM_NLINK];
   // joint limits
   real jnt_lo[ARM_NLINK], jnt_hi[ARM_NLINK], jnt_margin[ARM_NLINK], jnt_solref[ARM_NLINK][2], jnt_solimp[ARM_NLINK][5], jnt_diag[ARM_NLINK];
+  real jnt_kb[ARM_NLINK][2], pair_kb[ARM_MAXPAIR][2];  // reference stiffness / damping (mjs_kb of solref, solimp, timestep): constants of the model
   int jnt_limited[ARM_NLINK];
   // objects (free bodies, com at the body origin, principal axes = body axes)
   real obj_mass[ARM_MAXOBJ], obj_I[ARM_MAXOBJ][3];
@@ -306,6 +307,8 @@ int build_arm_model(const MjsModel& m, const MjsTask& t, int precision_f64, ArmM
   A.n_sub = t.n_sub; A.kind = t.kind; A.reward_type = t.reward_type; A.max_steps = t.max_steps;
   A.action_dim = t.action_dim; A.obs_dim = t.obs_dim; A.integrator = m.integrator; A.max_iter = m.solver_iterations;
   A.timestep = (real)m.timestep; A.impratio = (real)m.impratio;
+  for (int j = 0; j < ARM_NLINK; j++) mjs_kb<real>(A.jnt_solref[j], A.jnt_solimp[j], A.timestep, &A.jnt_kb[j][0], &A.jnt_kb[j][1]);
+  for (int q = 0; q < A.npair; q++) mjs_kb<real>(A.pair_solref[q], A.pair_solimp[q], A.timestep, &A.pair_kb[q][0], &A.pair_kb[q][1]);
   A.scale = (real)(1.0 / (m.meaninertia * (m.nv > 1 ? m.nv : 1)));
   // mjOption.tolerance as given (MuJoCo default 1e-8; parity tests pass 1e-12 to both sides); FP32 cannot resolve below 1e-6
   A.tol = precision_f64 ? (real)m.tolerance : (real)(m.tolerance > 1e-6 ? m.tolerance : 1e-6);

@@ -13,6 +13,9 @@
 #ifndef ARM_STEP_WPB_F64
 #define ARM_STEP_WPB_F64 12  // 12 x 19.3 KB of FP64 WarpMem fill the 227 KB of one SM; 168 regs x 384 threads fit the RF
 #endif
+#ifndef MJS_QUEUE_DEFAULT
+#define MJS_QUEUE_DEFAULT 0
+#endif
 #ifndef ARM_STEP_SYNC
 #define ARM_STEP_SYNC true
 #endif
@@ -28,6 +31,7 @@ struct ArmSim {
   ArmModel<float> mf;
   ArmModel<double> md;
   double* d_debug;
+  int* queue;     // work-item counter of the persistent step grid (queue mode)
   // pre-settled reset slots + side stream (tasks with settle steps)
   double* slot_sd;
   int* slot_si;
