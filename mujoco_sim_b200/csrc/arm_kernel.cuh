@@ -80,6 +80,8 @@ struct WarpMem {
   int ncon;
   int status;
   int sync;     // lock-step mode: all warps of the block pass the stage barriers together
+  int period;   // the substep-start barrier is taken every `period` substeps (1: every substep)
+  int novote;   // lock-step without the Newton loop: the stages before the solve stay aligned, the data-dependent iterations run free
   int coup;     // bit b: the arm block shares a contact with prop b
   int objcoup;  // non-zero: two props share a contact (dense factorisation path)
 #ifdef MJS_STAGE_CLOCKS
@@ -93,23 +95,62 @@ struct WarpMem {
 #define STAGE_CLK(W, k, t) do { } while (0)
 #endif
 // ------------------------------------------------------------------ warp helpers
+// Double shuffles split the value with __double2loint / __double2hiint (register-pair aliases, no instructions)
+// instead of the `asm volatile("mov.b64 ...")` of cuda's sm_30_intrinsics.hpp, which costs four real moves per shuffle
+// (ncu, profiles/r1: 300 of the 6.6 k instructions executed once per substep were those moves).
+__device__ __forceinline__ float shfl(float v, int src) { return __shfl_sync(FULLMASK, v, src); }
+__device__ __forceinline__ int shfl(int v, int src) { return __shfl_sync(FULLMASK, v, src); }
+__device__ __forceinline__ float shfl_up(float v, int d) { return __shfl_up_sync(FULLMASK, v, d); }
+__device__ __forceinline__ float shfl_down(float v, int d) { return __shfl_down_sync(FULLMASK, v, d); }
+__device__ __forceinline__ float shfl_xor(float v, int m) { return __shfl_xor_sync(FULLMASK, v, m); }
+#ifdef MJS_STOCK_SHFL
+__device__ __forceinline__ double shfl(double v, int src) { return __shfl_sync(FULLMASK, v, src); }
+__device__ __forceinline__ double shfl_up(double v, int d) { return __shfl_up_sync(FULLMASK, v, d); }
+__device__ __forceinline__ double shfl_down(double v, int d) { return __shfl_down_sync(FULLMASK, v, d); }
+__device__ __forceinline__ double shfl_xor(double v, int m) { return __shfl_xor_sync(FULLMASK, v, m); }
+#else
+#define MJS_SHFL64(NAME, OP)                                                          \
+  __device__ __forceinline__ double NAME(double v, int a) {                           \
+    int lo = OP(FULLMASK, __double2loint(v), a), hi = OP(FULLMASK, __double2hiint(v), a); \
+    return __hiloint2double(hi, lo);                                                  \
+  }
+MJS_SHFL64(shfl, __shfl_sync)
+MJS_SHFL64(shfl_up, __shfl_up_sync)
+MJS_SHFL64(shfl_down, __shfl_down_sync)
+MJS_SHFL64(shfl_xor, __shfl_xor_sync)
+#undef MJS_SHFL64
+#endif
 template <typename T>
 __device__ __forceinline__ T warp_sum(T v) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
+  for (int o = 16; o > 0; o >>= 1) v += shfl_xor(v, o);
   return v;
 }
-__device__ __forceinline__ float shfl(float v, int src) { return __shfl_sync(FULLMASK, v, src); }
-__device__ __forceinline__ double shfl(double v, int src) { return __shfl_sync(FULLMASK, v, src); }
-__device__ __forceinline__ int shfl(int v, int src) { return __shfl_sync(FULLMASK, v, src); }
-__device__ __forceinline__ float shfl_up(float v, int d) { return __shfl_up_sync(FULLMASK, v, d); }
-__device__ __forceinline__ double shfl_up(double v, int d) { return __shfl_up_sync(FULLMASK, v, d); }
-__device__ __forceinline__ float shfl_down(float v, int d) { return __shfl_down_sync(FULLMASK, v, d); }
-__device__ __forceinline__ double shfl_down(double v, int d) { return __shfl_down_sync(FULLMASK, v, d); }
 
 template <typename real> __device__ __forceinline__ void sincos_r(real x, real* s, real* c);
 template <> __device__ __forceinline__ void sincos_r<float>(float x, float* s, float* c) { sincosf(x, s, c); }
+#ifdef MJS_STOCK_SINCOS
 template <> __device__ __forceinline__ void sincos_r<double>(double x, double* s, double* c) { sincos(x, s, c); }
+#else
+// sin / cos of a joint half-angle or a quaternion increment in ~35 instructions instead of the ~160 of sincos(): two-constant
+// Cody-Waite reduction by pi/2 (exact enough for |x| < 1e5; the arguments here are bounded by the joint ranges) and the
+// fdlibm kernel polynomials on [-pi/4, pi/4].  Max error against libm over [-7, 7]: 1.1e-16 (tools/check_sincos.py).
+template <> __device__ __forceinline__ void sincos_r<double>(double x, double* s, double* c) {
+  double n = rint(x * 0.63661977236758134308);
+  double r = fma(-n, 1.5707963267948966, x);
+  r = fma(-n, 6.123233995736766e-17, r);
+  double z = r * r;
+  double ps = fma(z, fma(z, fma(z, fma(z, fma(z, 1.58969099521155010221e-10, -2.50507602534068634195e-08), 2.75573137070700676789e-06),
+                                -1.98412698298579493134e-04), 8.33333333332248946124e-03), -1.66666666666666324348e-01);
+  double pc = fma(z, fma(z, fma(z, fma(z, fma(z, -1.13596475577881948265e-11, 2.08757232129817482790e-09), -2.75573143513906633035e-07),
+                                2.48015872894767294178e-05), -1.38888888888741095749e-03), 4.16666666666666019037e-02);
+  double sr = fma(r * z, ps, r), cr = fma(z, fma(z, pc, -0.5), 1.0);
+  int k = (int)n;
+  double ss = (k & 1) ? cr : sr, cc = (k & 1) ? sr : cr;
+  *s = (k & 2) ? -ss : ss;
+  *c = ((k + 1) & 2) ? -cc : cc;
+}
+#endif
 template <typename real> __device__ __forceinline__ real rsqrt_r(real x);
 template <> __device__ __forceinline__ float rsqrt_r<float>(float x) { return rsqrtf(x); }
 // rsqrt(double): MUFU.RSQ64H seed + Newton steps (~1 ulp), a quarter of the instructions of 1.0 / sqrt(x)
@@ -1040,6 +1081,8 @@ struct ArmEngine {
     const real fsm_i = isdof ? W.fsm[lane] : (real)0;
     bool done = false;
     int nit = 0;
+    // lock-step Newton loop: the group iterates (and leaves) together; barriers inside the loop are legal only then
+    const bool vote = W.sync >= 2 && !W.novote;
     for (; it < A.max_iter; it++) {
       real Ma = 0, grad = 0, ccost = 0, cost = 0, gn = 0, dir_i = 0;
       if (!done) {
@@ -1061,7 +1104,7 @@ struct ArmEngine {
       }
       STAGE_CLK(W, 4, tclk);
       // lock-step mode: the block leaves the loop together (shared instruction fetch)
-      if (W.sync >= 2) { if (!group_or(!done)) break; }
+      if (vote) { if (!group_or(!done)) break; }
       else if (done) break;
       STAGE_CLK(W, 10, tclk);
       if (!done) {
@@ -1099,7 +1142,7 @@ struct ArmEngine {
         __syncwarp();
       }
       STAGE_CLK(W, 5, tclk);
-      stage_sync(W, 3);
+      if (vote) stage_sync(W, 3);
       if (!done) {
         real b = -grad;
         if (W.objcoup == 0) b = block_direction(W, lane, b);
@@ -1109,7 +1152,7 @@ struct ArmEngine {
         __syncwarp();
       }
       STAGE_CLK(W, 6, tclk);
-      stage_sync(W, 3);
+      if (vote) stage_sync(W, 3);
       if (!done) {
         // ---- exact line search along dir
         real Md = 0;
@@ -1283,7 +1326,7 @@ struct ArmEngine {
         double ax0 = 1, ax1 = 0, ax2 = 0;
         if (nrm >= MJS_MINVAL) { ax0 = w0 / nrm; ax1 = w1 / nrm; ax2 = w2 / nrm; }
         double ang = nrm * (double)h, sn, cs;
-        if (sizeof(real) == 8) sincos(0.5 * ang, &sn, &cs);
+        if (sizeof(real) == 8) sincos_r<double>(0.5 * ang, &sn, &cs);
         else { float fs, fc; sincosf((float)(0.5 * ang), &fs, &fc); sn = fs; cs = fc; }
         double dq[4] = {cs, ax0 * sn, ax1 * sn, ax2 * sn};
         double q[4] = {W.qpos[qa + 3], W.qpos[qa + 4], W.qpos[qa + 5], W.qpos[qa + 6]}, r[4];
@@ -1308,7 +1351,7 @@ struct ArmEngine {
     const AM& A = cmodel<real>();
     WM& W = *Wp;
     ConReg C;
-    stage_sync(W, 1);
+    if (!(do_integrate & 2)) stage_sync(W, 1);
     long long tclk = clock64(); (void)tclk;
 #ifdef MJS_STAGE_CLOCKS_REPEAT  // experiment: the same (non-inlined) stage twice; the second run is hot in the instruction cache
     kinematics_only(&W, lane);
@@ -1345,7 +1388,7 @@ struct ArmEngine {
     tclk = clock64();
     r.touch = touch_force(A, W, lane, C);
     stage_sync(W, 3);
-    if (do_integrate) integrate(A, W, lane, clamped, time);
+    if (do_integrate & 1) integrate(A, W, lane, clamped, time);
     STAGE_CLK(W, 9, tclk);
     r.a_i = a_i;
     r.time = time;
@@ -1527,7 +1570,7 @@ struct ArmTask {
     const int* si = io.si + (size_t)e * L::SI;
     T.step = si[L::I_STEP]; T.traj = si[L::I_TRAJ]; T.swa = si[L::I_SWA]; T.swp = si[L::I_SWP]; T.swc = si[L::I_SWC];
     T.status = si[L::I_STATUS]; T.episode = si[L::I_EPISODE]; T.len = si[L::I_LEN];
-    if (lane == 0) { W.status = 0; W.sync = sync; }
+    if (lane == 0) { W.status = 0; W.sync = sync & 7; W.novote = (sync >> 3) & 1; W.period = 1 + ((sync >> 4) & 15); }
 #ifdef MJS_STAGE_CLOCKS
     if (lane < MJS_NCLK) W.clk[lane] = 0;
 #endif
@@ -1666,7 +1709,7 @@ struct ArmTask {
     o.h4 = o.h8 = o.h16 = o.h32 = 0;
     for (int k = 0; k < A.n_sub; k++) {
       before_substep(A, W, lane, T);
-      typename E::SubRes so = E::substep(&W, lane, a_i, T.time, 1);
+      typename E::SubRes so = E::substep(&W, lane, a_i, T.time, (k % W.period) ? 3 : 1);  // bit 1: skip the substep-start barrier
       a_i = so.a_i; T.time = so.time;
       nit_sum += so.niter; nit_max = so.niter > nit_max ? so.niter : nit_max;
 #ifdef MJS_NIT_HIST
@@ -1860,7 +1903,7 @@ __device__ __noinline__ void arm_settle_job(const ArmModel<real>& A, WarpMem<rea
     if (T.episode != episode + 1) prog = 0;  // overtaken: start again for the right episode
   }
   if (prog == 0) {
-    if (lane == 0) { W.status = 0; W.sync = 0; }
+    if (lane == 0) { W.status = 0; W.sync = 0; W.novote = 0; W.period = 1; }
     T.episode = episode; T.swp = 0; T.status = 0;
     for (int k = 0; k < 3; k++) T.ovr[k] = io.sd[(size_t)e * L::SD + L::OVR + k];  // constant per env outside Button Push
     TK::reset_begin(A, W, lane, io, e, T, a_i);

@@ -3,17 +3,24 @@ usage: ncu -i rep --page source --print-source cuda,sass --csv | python tools/nc
 import csv, sys, collections
 units = float(sys.argv[1]); top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 rows = list(csv.reader(sys.stdin))
-STAGES = [(74, 95, "warp helpers (shfl, warp_sum, rsqrt)"), (96, 156, "vector helpers (cross, mat_vec, quat, spi_mul)"),
-          (194, 267, "kinematics"), (268, 411, "dynamics(CRB/RNE/act)"), (412, 635, "collide"), (636, 766, "make_rows"), (767, 801, "contact_eval"),
-          (802, 819, "contact_apply"), (820, 834, "jt_force"), (835, 937, "block_direction"), (938, 971, "dense_direction"), (972, 1126, "solve(body)"),
-          (1127, 1147, "touch"), (1148, 1220, "integrate"), (1221, 1256, "substep glue"), (1257, 1356, "ur_ik"), (1357, 2100, "task/io")]
+STAGES = [(96, 118, "warp helpers (shfl, warp_sum, rsqrt)"), (119, 180, "vector helpers (cross, mat_vec, quat, spi_mul)"),
+          (230, 303, "kinematics"), (304, 446, "dynamics(CRB/RNE/act)"), (447, 669, "collide"), (670, 799, "make_rows"), (800, 832, "contact_eval"),
+          (833, 850, "contact_apply"), (851, 870, "jt_force"), (871, 984, "block_direction"), (985, 1018, "dense_direction"), (1019, 1182, "solve(body)"),
+          (1183, 1205, "touch"), (1206, 1300, "integrate"), (1301, 1360, "substep glue"), (1361, 1510, "ur_ik"), (1511, 2200, "task/io")]
+import os
+SHIFT = [tuple(map(int, x.split(":"))) for x in os.environ.get("LINE_SHIFT", "").split(",") if x]  # "from:delta,..." for a profile of an older source
+def shifted(line):
+    d = 0
+    for lo, dd in SHIFT:
+        if line >= lo: d = dd
+    return line + d
 hd = None; per_line = collections.defaultdict(lambda: [0, 0, "", 0]); cur_file = ""
 for r in rows:
     if "Instructions Executed" in r and "Source" in r:
         hd = r; ie = r.index("Instructions Executed"); isamp = r.index("# Samples"); isrc = r.index("Source"); il = 0
         continue
     if hd is None or len(r) <= max(ie, isamp): continue
-    try: line = int(r[il]); ex = int(r[ie] or 0); sm = int(r[isamp] or 0)
+    try: line = shifted(int(r[il])); ex = int(r[ie] or 0); sm = int(r[isamp] or 0)
     except ValueError: continue
     p = per_line[line]; p[0] += ex; p[1] += sm; p[2] = r[isrc][:110]; p[3] += 1 if ex >= 0.9 * units else 0
 tot = sum(v[0] for v in per_line.values()); ts = sum(v[1] for v in per_line.values())
