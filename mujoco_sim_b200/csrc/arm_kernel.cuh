@@ -485,10 +485,21 @@ struct ArmEngine {
   // One lane per candidate pair: bounding-sphere broadphase, analytic narrowphase
   // (same routines as oracle/mjs_oracle.cpp), warp-scan compaction into W.craw.
   // Joint-limit rows ride along as pseudo-contacts (cpair = -1 - joint).
+  // Contact slot N (0..3, a run-time value) is written through a select chain over static indices so that cd[] / cp[][]
+  // stay in registers: a dynamically indexed array lives in the thread's stack frame, and the stack traffic of 384
+  // threads does not fit the 24 KB of L1 left beside 231 KB of shared memory.
+#define MJS_CPUT(N, D, X, Y, Z)                                                                       \
+  do {                                                                                                \
+    const real _d = (D), _x = (X), _y = (Y), _z = (Z);                                                \
+    _Pragma("unroll") for (int _s = 0; _s < 4; _s++)                                                  \
+      if (_s == (N)) { cd[_s] = _d; cp[_s][0] = _x; cp[_s][1] = _y; cp[_s][2] = _z; }                 \
+  } while (0)
   __device__ static void collide(const AM& A, WM& W, int lane) {
     int n = 0;
-    real cd[4], cp[4][3], nrm[3] = {0, 0, 1}, yh[3] = {0, 0, 0};
+    // (zero-initialised on purpose: ptxas keeps the arrays in registers only when every slot has a definite value)
+    real cd[4] = {0, 0, 0, 0}, cp[4][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}, {0, 0, 0}}, nrm[3] = {0, 0, 1}, yh[3] = {0, 0, 0};
     int code = lane;  // pair index; limits use -1 - j
+    unsigned valid = 0;  // slots that become contacts (bit k = slot k); their order is kept
     if (lane < A.npair) {
       int g1 = GM().pair_g1[lane], g2 = GM().pair_g2[lane];
       int t1 = GM().geom_type[g1], t2 = GM().geom_type[g2];
@@ -516,7 +527,7 @@ struct ArmEngine {
             real end[3] = {p2[0] + ax[0] * sg, p2[1] + ax[1] * sg, p2[2] + ax[2] * sg};
             real d3[3] = {end[0] - p1[0], end[1] - p1[1], end[2] - p1[2]};
             real dist = dot3(d3, nrm) - s2[0];
-            if (dist <= margin) { cd[n] = dist; for (int k = 0; k < 3; k++) cp[n][k] = end[k] - nrm[k] * (s2[0] + dist * (real)0.5); n++; }
+            if (dist <= margin) { const real hh = s2[0] + dist * (real)0.5; MJS_CPUT(n, dist, end[0] - nrm[0] * hh, end[1] - nrm[1] * hh, end[2] - nrm[2] * hh); n++; }
           }
         } else if (t1 == MJS_GEOM_PLANE && t2 == MJS_GEOM_CYLINDER) {
           real ax[3] = {m2[2], m2[5], m2[8]};
@@ -541,9 +552,9 @@ struct ArmEngine {
             n = 1;
             if (dist0 - prjaxis + prjvec <= margin) {
               d = dist0 - prjaxis + prjvec;
-              cd[n] = d;
-              for (int k = 0; k < 3; k++) cp[n][k] = p2[k] + vec[k] - ax[k] - nrm[k] * d * (real)0.5;
-              n++;
+              cd[1] = d;
+              for (int k = 0; k < 3; k++) cp[1][k] = p2[k] + vec[k] - ax[k] - nrm[k] * d * (real)0.5;
+              n = 2;
             }
             real prjvec1 = -prjvec * (real)0.5;
             if (dist0 + prjaxis + prjvec1 <= margin && n <= 2) {
@@ -553,13 +564,15 @@ struct ArmEngine {
               if (l < (real)MJS_MINVAL) { v1[0] = 1; v1[1] = 0; v1[2] = 0; } else { v1[0] /= l; v1[1] /= l; v1[2] /= l; }
               real s = s2[0] * (real)0.8660254037844386;  // sqrt(3)/2
               d = dist0 + prjaxis + prjvec1;
+              real pa[3], pb[3];
 #pragma unroll
-              for (int e = 0; e < 2; e++) {
-                real sg = e == 0 ? s : -s;
-                cd[n] = d;
-                for (int k = 0; k < 3; k++) cp[n][k] = p2[k] + v1[k] * sg + ax[k] - vec[k] * (real)0.5 - nrm[k] * d * (real)0.5;
-                n++;
+              for (int k = 0; k < 3; k++) {
+                pa[k] = p2[k] + v1[k] * s + ax[k] - vec[k] * (real)0.5 - nrm[k] * d * (real)0.5;
+                pb[k] = p2[k] + v1[k] * -s + ax[k] - vec[k] * (real)0.5 - nrm[k] * d * (real)0.5;
               }
+              if (n == 1) { cd[1] = d; cd[2] = d; for (int k = 0; k < 3; k++) { cp[1][k] = pa[k]; cp[2][k] = pb[k]; } }
+              else { cd[2] = d; cd[3] = d; for (int k = 0; k < 3; k++) { cp[2][k] = pa[k]; cp[3][k] = pb[k]; } }
+              n += 2;
             }
           }
         } else if (t1 == MJS_GEOM_PLANE && t2 == MJS_GEOM_BOX) {
@@ -569,8 +582,8 @@ struct ArmEngine {
             mat_vec(corner, m2, vloc);
             real ldist = dot3(nrm, corner);
             if (dist + ldist > margin || ldist > 0) continue;
-            cd[n] = dist + ldist;
-            for (int k = 0; k < 3; k++) cp[n][k] = corner[k] + p2[k] - nrm[k] * cd[n] * (real)0.5;
+            const real dc = dist + ldist;
+            MJS_CPUT(n, dc, corner[0] + p2[0] - nrm[0] * dc * (real)0.5, corner[1] + p2[1] - nrm[1] * dc * (real)0.5, corner[2] + p2[2] - nrm[2] * dc * (real)0.5);
             n++;
           }
         } else {
@@ -658,11 +671,10 @@ struct ArmEngine {
         }
         // mj_collision: contacts with dist >= margin - gap produce no rows
         real incl = GM().pair_incl[lane];
-        int m = 0;
 #pragma unroll
         for (int k = 0; k < 4; k++)
-          if (k < n && cd[k] < incl) { cd[m] = cd[k]; cp[m][0] = cp[k][0]; cp[m][1] = cp[k][1]; cp[m][2] = cp[k][2]; m++; }
-        n = m;
+          if (k < n && cd[k] < incl) valid |= 1u << k;
+        n = __popc(valid);
       }
     } else if (lane >= A.npair && lane < A.npair + ARM_NLINK) {
       // joint limits (mj_instantiateLimit)
@@ -670,8 +682,8 @@ struct ArmEngine {
       if (GM().jnt_limited[j]) {
         real q = (real)W.qpos[j];
         real dlo = q - GM().jnt_lo[j], dhi = GM().jnt_hi[j] - q;
-        if (dlo < GM().jnt_margin[j]) { n = 1; cd[0] = dlo; cp[0][0] = 1; }
-        else if (dhi < GM().jnt_margin[j]) { n = 1; cd[0] = dhi; cp[0][0] = -1; }
+        if (dlo < GM().jnt_margin[j]) { n = 1; valid = 1; cd[0] = dlo; cp[0][0] = 1; }
+        else if (dhi < GM().jnt_margin[j]) { n = 1; valid = 1; cd[0] = dhi; cp[0][0] = -1; }
         cp[0][1] = 0; cp[0][2] = 0;
         code = -1 - j;
       }
@@ -685,8 +697,8 @@ struct ArmEngine {
     if (total > ARM_MAXC) { if (lane == 0) atomicOr(&W.status, MJS_STATUS_CONTACT_OVERFLOW); total = ARM_MAXC; }
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-      if (k < n && base + k < ARM_MAXC) {
-        int c = base + k;
+      const int c = base + __popc(valid & ((1u << k) - 1u));
+      if (((valid >> k) & 1u) && c < ARM_MAXC) {
         W.craw[0][c] = cd[k];
         W.craw[1][c] = cp[k][0]; W.craw[2][c] = cp[k][1]; W.craw[3][c] = cp[k][2];
         W.craw[4][c] = nrm[0]; W.craw[5][c] = nrm[1]; W.craw[6][c] = nrm[2];
@@ -760,6 +772,7 @@ struct ArmEngine {
           int slot = GM().geom_slot[g];
           real sg = side == 0 ? (real)-1 : (real)1;
           int blk = -1, cols = 0;
+#ifdef MJS_ROWS_V1
           if (slot >= SLOT_LINK0 && slot < SLOT_LINK0 + ARM_NLINK) {
             blk = 0; cols = slot - SLOT_LINK0 + 1;
             for (int j = 0; j < cols; j++) {
@@ -793,6 +806,58 @@ struct ArmEngine {
               }
             }
           }
+#else
+          // Row loops are unrolled with `k < nrow` guards so that fr[] and u[] are indexed statically (registers, not the
+          // thread's stack frame), and the lever-arm cross product of a column is formed once, not once per row.
+          if (slot >= SLOT_LINK0 && slot < SLOT_LINK0 + ARM_NLINK) {
+            blk = 0; cols = slot - SLOT_LINK0 + 1;
+            for (int j = 0; j < cols; j++) {
+              real Sa[3] = {W.S[j][0], W.S[j][1], W.S[j][2]}, jp[3];
+              cross3(jp, Sa, pos);
+              jp[0] += W.S[j][3]; jp[1] += W.S[j][4]; jp[2] += W.S[j][5];
+              const real w = W.qv[j];
+#pragma unroll
+              for (int k = 0; k < 4; k++) {
+                if (k < nrow) {
+                  real val = k < 3 ? dot3(fr + 3 * k, jp) : dot3(fr, Sa);
+                  W.cJ[(side * 4 + k) * 6 + j][c] = sg * val;
+                  u[k] += sg * val * w;
+                }
+              }
+            }
+          } else if (slot >= SLOT_OBJ0 && slot < SLOT_OBJ0 + ARM_MAXOBJ) {
+            int ob = slot - SLOT_OBJ0;
+            blk = 1 + ob; cols = 6;
+            const real* R = W.xmat[slot];
+            real r[3] = {pos[0] - W.xpos[slot][0], pos[1] - W.xpos[slot][1], pos[2] - W.xpos[slot][2]};
+            int b0 = ARM_NLINK + 6 * ob;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+              if (k < nrow) {
+#pragma unroll
+                for (int j = 0; j < 3; j++) {
+                  real val = k < 3 ? fr[3 * k + j] : (real)0;
+                  W.cJ[(side * 4 + k) * 6 + j][c] = sg * val;
+                  u[k] += sg * val * W.qv[b0 + j];
+                }
+              }
+            }
+#pragma unroll ROLL
+            for (int j = 0; j < 3; j++) {
+              real Ra[3] = {R[j], R[3 + j], R[6 + j]}, jp[3];
+              cross3(jp, Ra, r);
+              const real w = W.qv[b0 + 3 + j];
+#pragma unroll
+              for (int k = 0; k < 4; k++) {
+                if (k < nrow) {
+                  real val = k < 3 ? dot3(fr + 3 * k, jp) : dot3(fr, Ra);
+                  W.cJ[(side * 4 + k) * 6 + 3 + j][c] = sg * val;
+                  u[k] += sg * val * w;
+                }
+              }
+            }
+          }
+#endif
           W.cblk[side][c] = blk; W.ccols[side][c] = cols;
         }
         C.mu[0] = GM().pair_mu[p][0]; C.mu[1] = GM().pair_mu[p][0]; C.mu[2] = GM().pair_mu[p][1];
