@@ -69,8 +69,9 @@ static ArmIO make_io(ArmSim* a) {
   memset(&io, 0, sizeof(io));
   // Lock-step of the step kernel's warp groups (shared instruction fetch): 0 none; 1 barrier at substep start; 2 + before the
   // solve and a group vote per Newton iteration; 3 + every stage; +8: levels 2/3 without the vote (the data-dependent Newton
-  // loop runs free).  Defaults measured on B200 (profiles/r1/sync_modes.txt): f64 -> 1, FP32 -> 2 + 8.
-  { const char* lv = getenv("MJS_SYNC_LEVEL"); io.sync_level = lv ? atoi(lv) : (a->precision == 0 ? 1 : 10); }
+  // loop runs free), +16 (P - 1): the substep-start barrier every P-th substep.  Default measured on B200
+  // (profiles/r1/sync_modes.txt, exp9): level 1 for both precisions.
+  { const char* lv = getenv("MJS_SYNC_LEVEL"); io.sync_level = lv ? atoi(lv) : 1; }
   io.sd = a->sd; io.si = a->si; io.stats = a->d_stats;
   io.slot_sd = a->slot_sd; io.slot_si = a->slot_si; io.slot_obs = a->slot_obs; io.slot_ready = a->slot_ready; io.slot_prog = a->slot_prog; io.times = a->d_times; io.N = a->N; io.seed = a->seed; io.env_offset = a->env_offset;
   return io;

@@ -1175,6 +1175,7 @@ struct ArmEngine {
       if (!done) {
         nit++;
         // ---- Hessian rows H = M + sum_c Jc^T W_c Jc (solver ordering)
+#ifdef MJS_HESS_V1
         if (isdof) {
           for (int j = 0; j < NV; j++) W.H[si][j] = 0;
           if (lane < ARM_NLINK) {
@@ -1204,6 +1205,56 @@ struct ArmEngine {
             }
           }
         }
+#else
+        // The row's own diagonal block accumulates in registers and is stored once; entries outside the block exist only
+        // when a contact couples two blocks (coup / objcoup), and only then is the row cleared and updated in shared memory
+        // (block_direction never reads an off-block entry of an uncoupled Hessian).
+        if (isdof) {
+          const int ownbase = lane < ARM_NLINK ? 6 * NOBJ : (myblk - 1) * 6;
+          real hown[6];
+#pragma unroll
+          for (int j = 0; j < 6; j++) hown[j] = lane < ARM_NLINK ? W.Marm[lane][j] : (j == d ? mdiag : (real)0);
+          if ((W.coup | W.objcoup) != 0)
+            for (int j = 0; j < NV; j++) W.H[si][j] = 0;
+          int n = W.bcount[myblk];
+          for (int r = 0; r < n; r++) {
+            int e = W.blist[myblk][r], c = e & 0xff, side = e >> 8;
+            real jm[4], z[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) jm[k] = W.cJ[(side * 4 + k) * 6 + d][c];
+            z[0] = W.cW[0][c] * jm[0] + W.cW[1][c] * jm[1] + W.cW[2][c] * jm[2] + W.cW[3][c] * jm[3];
+#pragma unroll
+            for (int k = 0; k < 3; k++) z[1 + k] = W.cW[1 + k][c] * jm[0] + W.cW[4 + k][c] * jm[1 + k];
+#pragma unroll ROLL
+            for (int s2 = 0; s2 < 2; s2++) {
+              int blk2 = W.cblk[s2][c];
+              if (blk2 < 0) continue;
+              int cols2 = W.ccols[s2][c];
+              if (blk2 == myblk) {
+#pragma unroll
+                for (int j = 0; j < 6; j++) {
+                  if (j < cols2) {
+                    real t = 0;
+#pragma unroll
+                    for (int k = 0; k < 4; k++) t += z[k] * W.cJ[(s2 * 4 + k) * 6 + j][c];
+                    hown[j] += t;
+                  }
+                }
+              } else {
+                int b2 = blk_base(blk2);
+                for (int j = 0; j < cols2; j++) {
+                  real t = 0;
+#pragma unroll
+                  for (int k = 0; k < 4; k++) t += z[k] * W.cJ[(s2 * 4 + k) * 6 + j][c];
+                  W.H[si][sidx(b2 + j)] += t;
+                }
+              }
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 6; j++) W.H[si][ownbase + j] = hown[j];
+        }
+#endif
         __syncwarp();
       }
       STAGE_CLK(W, 5, tclk);
