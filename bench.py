@@ -31,7 +31,7 @@ WORKLOADS = {
     "push_button": ("robot_push_button", 4736, 0.58e6, 539.0),
 }
 METRIC = "env-steps/s (device-timed) Planar Push"
-TRAFFIC_PER_ENV = {"f64": 5206.0, "mixed": 5206.0}  # ncu at 42624 envs: (45.2 MB read + 176.7 MB written) / launch; measured at f64, the mixed kernel moves the same FP64 records
+TRAFFIC_PER_ENV = {"f64": 3158.0, "mixed": 3158.0}  # ncu at 42624 envs: (38.3 MB read + 96.3 MB written) / launch; measured at f64, the mixed kernel moves the same FP64 records
 MIXED_ENVS = 37888  # 148 SMs x 16 FP32 warps x 16 waves
 FP32_PEAK_TFLOPS_FALLBACK = 148 * 128 * 2 * 1.965e9 / 1e12  # SMs x FP32 lanes x FMA x clocks.max.sm = 74.4
 
@@ -325,7 +325,7 @@ def run_gpu(args):
             "roofline": {"bound": bound, "achieved": kern_rate * flops_per / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": kern_rate * flops_per / 1e12 / fp32_peak,
                          "traffic": (TRAFFIC_PER_ENV[args.precision] * N if args.workload == "planar_push" else None),
-                         "traffic_note": "DRAM bytes per launch = 5.2 kB/env (dram__bytes_read+write of one ncu --set full capture of the bench command at 42624 envs, profiles/r1/prof_f64_v6_raw.csv; mostly write-back of the per-thread stack frames, 3.2 kB/env at 5328 envs) x envs; algorithmic 771 B/env",
+                         "traffic_note": "DRAM bytes per launch = 3.2 kB/env (dram__bytes_read+write of one ncu --set full capture of the bench command at 42624 envs, profiles/r1/prof_f64_v7_raw.csv: state records in and out, reset slots, outputs, write-back of the remaining per-thread stack traffic) x envs; algorithmic 771 B/env",
                          "kernel": "arm_step_kernel", "kernel_ms": kernel_ms, "kernel_ms_median": per[len(per) // 2], "flops_per_env_step": flops_per,
                          "peak_source": f"148 SMs x {lanes} {bound.upper()} lanes x 2 x clocks.max.sm {sm_max:.0f} MHz, nominal non-tensor FMA peak (MEASURED_PEAKS.json has only HBM and bf16 tensor peaks)",
                          "hbm": {"achieved": kern_rate * bytes_per / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": kern_rate * bytes_per / 1e9 / hbm_peak,

@@ -3,10 +3,11 @@ usage: ncu -i rep --page source --print-source cuda,sass --csv | python tools/nc
 import csv, sys, collections
 units = float(sys.argv[1]); top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 rows = list(csv.reader(sys.stdin))
-STAGES = [(96, 118, "warp helpers (shfl, warp_sum, rsqrt)"), (119, 180, "vector helpers (cross, mat_vec, quat, spi_mul)"),
-          (230, 303, "kinematics"), (304, 446, "dynamics(CRB/RNE/act)"), (447, 669, "collide"), (670, 799, "make_rows"), (800, 832, "contact_eval"),
-          (833, 850, "contact_apply"), (851, 870, "jt_force"), (871, 984, "block_direction"), (985, 1018, "dense_direction"), (1019, 1182, "solve(body)"),
-          (1183, 1205, "touch"), (1206, 1300, "integrate"), (1301, 1360, "substep glue"), (1361, 1510, "ur_ik"), (1511, 2200, "task/io")]
+# line ranges of csrc/arm_kernel.cuh at the commit the profile was taken from (update when the file moves; LINE_SHIFT maps an older profile)
+STAGES = [(97, 160, "warp helpers (shfl, warp_sum, sincos, rsqrt)"), (161, 225, "vector helpers (cross, mat_vec, quat, spi_mul)"),
+          (271, 344, "kinematics"), (345, 496, "dynamics(CRB/RNE/act)"), (497, 722, "collide"), (723, 905, "make_rows"), (906, 938, "contact_eval"),
+          (939, 956, "contact_apply"), (957, 976, "jt_force"), (977, 1090, "block_direction"), (1091, 1124, "dense_direction"), (1125, 1341, "solve(body)"),
+          (1342, 1364, "touch"), (1365, 1459, "integrate"), (1460, 1520, "substep glue"), (1521, 1670, "ur_ik"), (1671, 2400, "task/io")]
 import os
 SHIFT = [tuple(map(int, x.split(":"))) for x in os.environ.get("LINE_SHIFT", "").split(",") if x]  # "from:delta,..." for a profile of an older source
 def shifted(line):
