@@ -219,9 +219,10 @@ int mjs_step(MjsSim* s, const float* d_actions, float* d_obs, float* d_reward, u
   cudaStream_t st = (cudaStream_t)stream;
   if (s->task.kind == MJS_TASK_POINTMASS) {
     PmIO io = pm_io(s, d_actions, d_obs, d_reward, d_flags, d_final_obs, autoreset);
-    int grid = (s->N + 127) / 128;
-    if (s->precision == MJS_PRECISION_F64) pm_step_kernel<double><<<grid, 128, 0, st>>>(s->pm_pd, io);
-    else pm_step_kernel<float><<<grid, 128, 0, st>>>(s->pm_pf, io);
+    // one warp per block: 65 536 envs are 2048 blocks = 13.8 per SM (blocks of 128 threads: 3.5 per SM, a 15 % imbalance between SMs)
+    int grid = (s->N + 31) / 32;
+    if (s->precision == MJS_PRECISION_F64) pm_step_kernel<double><<<grid, 32, 0, st>>>(s->pm_pd, io);
+    else pm_step_kernel<float><<<grid, 32, 0, st>>>(s->pm_pf, io);
     s->launches++;
   } else {
     int r = arm_step(s->arm, d_actions, d_obs, d_reward, d_flags, d_final_obs, autoreset, s->step_index, st);

@@ -320,7 +320,7 @@ __global__ void __launch_bounds__(128) pm_step_kernel(PmParams<real> P, PmIO io)
     io.si[PM_I_STEPS * N + e] = steps;
   }
   // episode statistics: warp-reduce, one atomic per warp that finished an episode
-  if (io.stats) {
+  if (io.stats && __any_sync(0xffffffffu, n_ep > 0)) {  // warp-uniform: most steps no env of the warp finishes an episode
     unsigned full = 0xffffffffu;
     for (int off = 16; off > 0; off >>= 1) {
       ret_sum += __shfl_down_sync(full, ret_sum, off); len_sum += __shfl_down_sync(full, len_sum, off);
