@@ -9,5 +9,5 @@ $CMD > gpurun_out/plain2_$P.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:arm_step_kernel -s 4 -c 1 -o /tmp/prof_$P -f $CMD > gpurun_out/ncu_full_$P.log 2>&1
 ncu -i /tmp/prof_$P.ncu-rep --page raw --csv > gpurun_out/prof_${P}_raw.csv 2>/dev/null
 ncu -i /tmp/prof_$P.ncu-rep --page source --csv > gpurun_out/prof_${P}_source.csv 2>/dev/null
-ncu -i /tmp/prof_$P.ncu-rep --page source --print-source cuda,sass --csv 2>/dev/null > /tmp/prof_${P}_cuda.csv; head -c 3000 /tmp/prof_${P}_cuda.csv > gpurun_out/prof_${P}_cuda_head.csv; python tools/ncu_lines2.py ${UNITS:-94720} 45 < /tmp/prof_${P}_cuda.csv > gpurun_out/prof_${P}_lines.txt 2>&1
+ncu -i /tmp/prof_$P.ncu-rep --page source --print-source cuda,sass --csv 2>/dev/null > /tmp/prof_${P}_cuda.csv; head -c 3000 /tmp/prof_${P}_cuda.csv > gpurun_out/prof_${P}_cuda_head.csv; python tools/ncu_lines2.py ${UNITS:-852480} 45 < /tmp/prof_${P}_cuda.csv > gpurun_out/prof_${P}_lines.txt 2>&1
 ls -la /tmp/prof_$P.ncu-rep gpurun_out/prof_${P}_*.csv
