@@ -47,6 +47,17 @@ int mjs_reset(MjsSim* sim, const unsigned char* d_mask, float* d_obs, void* stre
 int mjs_step(MjsSim* sim, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags,
              float* d_final_obs, int autoreset, void* stream);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments and results as mjs_step,
+ * but the launch's scratch (Planar Push's settle-job list) lives in a file-scope static __device__ array of
+ * MJS_NOALLOC_MAX_JOBS = 16384 entries (66 KB, held by every GPU that loads the library until exit) instead of memory
+ * allocated for the simulator; the call runs no cudaMalloc / cudaFree.  Limit: num_envs * 3 / 100 + 1 <= 16384
+ * (num_envs <= 546 100); larger simulators get a clear error (-1).  The array is shared by all simulators and calls on a
+ * device: calls that overlap on the GPU (different streams, no ordering) race on it.  Tasks whose step uses no scratch
+ * (PointMass, Reach, Button Push, autoreset == 0) are forwarded to mjs_step, which allocates nothing either. */
+int mjs_step_noalloc(MjsSim* sim, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags,
+                     float* d_final_obs, int autoreset, void* stream);
+
 /* Same call with HOST buffers: copies actions H2D, steps, copies results D2H and
  * synchronises.  This is the end-to-end call the reference-side stub uses. */
 int mjs_step_host(MjsSim* sim, const float* h_actions, float* h_obs, float* h_reward, unsigned char* h_flags,

@@ -234,6 +234,16 @@ int mjs_step(MjsSim* s, const float* d_actions, float* d_obs, float* d_reward, u
   return 0;
 }
 
+int mjs_step_noalloc(MjsSim* s, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags, float* d_final_obs, int autoreset, void* stream) {
+  if (!s->arm) return mjs_step(s, d_actions, d_obs, d_reward, d_flags, d_final_obs, autoreset, stream);  // PointMass: the step uses no scratch and allocates nothing
+  int r = arm_step_noalloc(s->arm, d_actions, d_obs, d_reward, d_flags, d_final_obs, autoreset, s->step_index, (cudaStream_t)stream);
+  if (r < 0) return r;
+  s->launches += r;
+  s->step_index++;
+  MJS_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
 static int ensure_pin(MjsSim* s) {
   if (s->h_pin) return 0;
   size_t n = (size_t)s->N * (s->task.action_dim + 2 * s->task.obs_dim + 1) * sizeof(float) + 4 * (size_t)s->N + s->N;

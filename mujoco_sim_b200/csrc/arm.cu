@@ -138,6 +138,42 @@ int arm_step(ArmSim* a, const float* d_actions, float* d_obs, float* d_reward, u
   return dispatch(a, 0, io, st);
 }
 
+// ---- mjs_step_noalloc: the step launch with its scratch (the settle-job list of Planar Push) in a file-scope device array
+// instead of the simulator's cudaMalloc'ed one.  Added for callers that cannot
+// allocate (CUDA graph capture, serving loops); the reference has no counterpart.  The array is shared by every simulator
+// and every call on a device and keeps the last call's contents: the two counters are cleared on the stream before each
+// launch, the list entries are written before they are read.  Calls that overlap on the GPU race on it.
+#define MJS_NOALLOC_MAX_JOBS 16384  // list entries; a simulator needs num_envs * 3 / 100 + 1 of them (num_envs <= 546 100)
+static __device__ __align__(256) int g_noalloc_jobs[MJS_NOALLOC_MAX_JOBS + 64 + 2];
+static int* g_noalloc_ptr[64];  // device address of the array, per device (the symbol's host-side name is not an address)
+
+int arm_step_noalloc(ArmSim* a, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags, float* d_final_obs, int autoreset,
+                     unsigned int step_index, cudaStream_t st) {
+  if (!(a->slot_ready && autoreset)) return arm_step(a, d_actions, d_obs, d_reward, d_flags, d_final_obs, autoreset, step_index, st);  // no scratch on this path
+  if (a->job_cap > MJS_NOALLOC_MAX_JOBS) {
+    mjs_set_error("mjs_step_noalloc: %d envs need %d settle-job entries, the static scratch holds %d (num_envs <= %d)", a->N, a->job_cap,
+                  MJS_NOALLOC_MAX_JOBS, (MJS_NOALLOC_MAX_JOBS - 1) * 100 / 3);
+    return -1;
+  }
+  int dev = 0;
+  MJS_CUDA_CHECK(cudaGetDevice(&dev));
+  if (!g_noalloc_ptr[dev & 63]) {  // set-up, once per device, with that device current
+    int* p = nullptr;
+    MJS_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_noalloc_jobs));
+    g_noalloc_ptr[dev & 63] = p;
+  }
+  int* base = g_noalloc_ptr[dev & 63];
+  ArmIO io = make_io(a);
+  io.actions = d_actions; io.obs = d_obs; io.reward = d_reward; io.flags = d_flags; io.final_obs = d_final_obs;
+  io.autoreset = autoreset; io.step_index = step_index;
+  if (a->refill_pending) { MJS_CUDA_CHECK(cudaStreamWaitEvent(st, a->ev_refill, 0)); a->refill_pending = 0; }
+  int* counters = base + MJS_NOALLOC_MAX_JOBS + 64;
+  MJS_CUDA_CHECK(cudaMemsetAsync(counters, 0, 2 * sizeof(int), st));  // another simulator's call may have left them non-zero
+  io.jobs = base; io.job_cap = a->job_cap;
+  io.njobs = counters; io.njobs_next = counters + 1;
+  return dispatch(a, 0, io, st);
+}
+
 // make `st` wait for the refill work in flight (bench: close the timed region)
 int arm_join_aux(ArmSim* a, cudaStream_t st) {
   if (a->slot_ready && a->refill_pending) MJS_CUDA_CHECK(cudaStreamWaitEvent(st, a->ev_refill, 0));

@@ -15,3 +15,5 @@ int arm_join_aux(ArmSim* a, cudaStream_t st);
 int arm_debug_substeps(ArmSim* a, int k);
 int arm_debug_times(ArmSim* a, long long* h_out, int n);
 int arm_demo_policy(ArmSim* a, double noise, unsigned int step_index, float* d_actions, int* d_ok, cudaStream_t st);
+int arm_step_noalloc(ArmSim* a, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags, float* d_final_obs, int autoreset,
+                     unsigned int step_index, cudaStream_t st);
