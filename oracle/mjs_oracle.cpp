@@ -1402,6 +1402,10 @@ void write_obs_reward(const MjsModel* m, const MjsTask* t, MjsEnvState* s, const
   s->ep_return += reward;
 }
 
+// touch-sensor force after every substep of the last control_step on this thread (test hook: margin of the 5 N / 200 N
+// thresholds of switch.py:51-60, so flag comparisons can exclude envs that sit on a threshold)
+static thread_local double g_touch_trace[64];
+
 void control_step(const MjsModel* m, const MjsTask* t, MjsEnvState* s, const double* action, MjsStepOut* out, double tol_scale, long* flops) {
   static thread_local Data d;
   d.status = 0; d.flops = 0;
@@ -1427,6 +1431,7 @@ void control_step(const MjsModel* m, const MjsTask* t, MjsEnvState* s, const dou
     before_substep(t, s);
     step2(m, s, &d, false, true, tol_scale);
     step1(m, s, &d);
+    if (k < 64) g_touch_trace[k] = d.touch;
     if (t->kind == MJS_TASK_BUTTON) switch_update(t, s, d.touch);
   }
   // ---- after_step
@@ -1455,6 +1460,14 @@ extern "C" {
 // one control step for n envs (AoS states), OpenMP-free; callers thread by range
 void oracle_control_step(const MjsModel* m, const MjsTask* t, MjsEnvState* states, const double* actions, MjsStepOut* outs, int n, double tol_scale, long* flops) {
   for (int e = 0; e < n; e++) control_step(m, t, states + e, actions + (size_t)e * t->action_dim, outs + e, tol_scale, flops);
+}
+
+// oracle_control_step that also returns the touch-sensor force after every substep: touch[n][n_sub]
+void oracle_control_step_touch(const MjsModel* m, const MjsTask* t, MjsEnvState* states, const double* actions, MjsStepOut* outs, int n, double tol_scale, double* touch) {
+  for (int e = 0; e < n; e++) {
+    control_step(m, t, states + e, actions + (size_t)e * t->action_dim, outs + e, tol_scale, nullptr);
+    for (int k = 0; k < t->n_sub && k < 64; k++) touch[(size_t)e * t->n_sub + k] = g_touch_trace[k];
+  }
 }
 
 // finish a reset whose (qpos, qvel, mocap, ctrl, target...) were written by the caller:

@@ -66,6 +66,16 @@ class OracleEnvs:
         )
         return self.collect()
 
+    def step_touch(self, actions):
+        """step() that also returns the touch-sensor force after every substep: (collect(), touch[n, n_sub])"""
+        a = np.ascontiguousarray(actions, dtype=np.float64).reshape(self.n, self.task.action_dim)
+        touch = np.zeros((self.n, self.task.n_sub))
+        lib().oracle_control_step_touch(
+            ctypes.byref(self.model), ctypes.byref(self.task), self.states, _dp(a), self.outs, self.n,
+            ctypes.c_double(self.tol_scale), _dp(touch),
+        )
+        return self.collect(), touch
+
     def step_raw(self, actions):
         """step without gathering outputs into numpy (timed CPU baseline: no Python in the loop)"""
         a = np.ascontiguousarray(actions, dtype=np.float64).reshape(self.n, self.task.action_dim)

@@ -1,0 +1,190 @@
+"""GPU parity on the configuration bench.py measures (VERDICT r1 "weak" item 2): the CUDA side runs the DEFAULT
+mjOption.tolerance (1e-8, never overridden by the reference) and, for Planar Push, autoreset with slot adoption and
+settle jobs active; the oracle runs a 1e-12 solve from identical states.  Plus the f64 Button Push suite (item 3):
+exact pressed / active / success / termination flags on a 1024-env scripted rollout that presses the button, reaches the
+end pose and terminates.  All through the C ABI."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+from tests.helpers import arm_states, copy_states, push_states
+
+pytestmark = pytest.mark.gpu
+
+TOL_CONTACT_STEP = 1e-4
+
+
+def _qv(env, nq, nv):
+    st = env.get_state()
+    return np.array([list(s.qpos)[:nq] for s in st]), np.array([list(s.qvel)[:nv] for s in st]), st
+
+
+def test_push_default_tolerance_single_step_gate_on_4096_struck_env_steps():
+    """Single-step error from identical states <= 1e-4 with the CUDA solver at MuJoCo's default tolerance 1e-8 (the setting
+    of the timed run) against the oracle's 1e-12 minimiser; the pusher is driven into a prop on every step.
+
+    Soft contacts switch on discontinuously (a contact that appears at dist = 0 with approach velocity v carries the damping
+    force D b v at once), so a step in which a contact's distance crosses zero within the two sides' rounding difference is
+    amplified by ~1e5: measured on B200, 2 of 12 288 env-steps (probe: tools/gpu_tol_probe2.py; the same two appear with the
+    CUDA solver at 1e-12, so the tolerance is not the cause).  The oracle shows the same sensitivity against itself when its
+    input state is perturbed by 1e-9 (counted below).  Gate: every env-step within 1e-4 except at most 0.05 % such events."""
+    import mujoco_sim_b200 as ms
+    from mujoco_sim_b200.model.tasks import build_planar_push
+    from oracle.oracle import OracleEnvs
+
+    n, steps, b = 1024, 12, build_planar_push()
+    ora = push_states(b, n, 41)
+    pert = OracleEnvs(b, n)
+    env = ms.make("robot_planar_push", n, precision="f64", autoreset=False)  # solver_tolerance left at the model default
+    assert abs(b.model.tolerance - 1e-8) < 1e-20
+    rng = np.random.RandomState(42)
+    dq, dr, moved, dself = [], [], [], []
+    for k in range(steps):
+        env.set_state(copy_states(ora.states, n), forward=False)
+        ctypes.memmove(pert.states, ora.states, ctypes.sizeof(ora.states))
+        for e in range(n):  # the oracle against itself from a state perturbed by 1e-9 (props' positions)
+            for i in (6, 7, 13, 14, 20, 21):
+                pert.states[e].qpos[i] += rng.uniform(-1e-9, 1e-9)
+        qp = ora.field("qpos", 27)
+        prop = 6 + 7 * (k % 3)
+        a = (qp[:, prop:prop + 2] + rng.uniform(-0.01, 0.01, (n, 2))).astype(np.float32)
+        before = qp[:, 6:].copy()
+        obs_o, rew_o, _, fl_o = ora.step(a.astype(np.float64))
+        pert.step(a.astype(np.float64))
+        obs, rew, *_ = env.step(torch.from_numpy(a).cuda())
+        q, v, _ = _qv(env, 27, 24)
+        qo = ora.field("qpos", 27)
+        dq.append(np.abs(q - qo).max(1)); dr.append(np.abs(rew.cpu().numpy() - rew_o)); dself.append(np.abs(pert.field("qpos", 27) - qo).max(1))
+        moved.append(np.abs(qo[:, 6:] - before).max(1) > 1e-4)
+        np.testing.assert_array_equal(env._flags.cpu().numpy(), fl_o)
+    dq, dr, moved, dself = np.concatenate(dq), np.concatenate(dr), np.concatenate(moved), np.concatenate(dself)
+    out = dq > TOL_CONTACT_STEP
+    print("push f64, CUDA tol 1e-8 vs oracle 1e-12: env-steps", dq.size, "struck", int(moved.sum()), "p50 %.1e p99 %.1e p99.9 %.1e max %.1e" %
+          (np.percentile(dq, 50), np.percentile(dq, 99), np.percentile(dq, 99.9), dq.max()), "env-steps over 1e-4:", int(out.sum()),
+          "| oracle vs itself perturbed by 1e-9: over 1e-4:", int((dself > TOL_CONTACT_STEP).sum()), "max %.1e" % dself.max(), "| max|dreward| %.1e" % dr.max())
+    assert moved.sum() >= 4096
+    assert out.sum() <= dq.size // 2000 and moved[out].all()   # rare contact-onset events, struck props only
+    assert np.percentile(dq, 99.9) < TOL_CONTACT_STEP * 1e-2 and dq[~out].max() < TOL_CONTACT_STEP and dr.max() < TOL_CONTACT_STEP
+    env.close()
+
+
+def test_push_autoreset_rollout_across_episode_boundaries_matches_the_oracle():
+    """Free-running rollout with autoreset ON (default tolerance): the first boundary adopts the slots pre-settled after
+    mjs_reset, later ones mix inline resets and job-warp slots.  The oracle follows through every reset by re-sampling the
+    episode with the Python restatement of the device Philox stream (tests/philox_ref.py) and settling it itself.  Flags
+    and final observations are compared exactly (envs within 1e-6 of the target-radius threshold excluded and counted)."""
+    import mujoco_sim_b200 as ms
+    from mujoco_sim_b200.model.cstruct import MjsEnvState
+    from mujoco_sim_b200.model.tasks import RobotPushConfig, build_planar_push
+    from oracle.oracle import OracleEnvs
+    from tests.philox_ref import push_reset_state
+
+    n, seed, steps, radius = 384, 31, 14, 0.12
+    cfg = RobotPushConfig(max_control_steps_per_episode=6, target_radius=radius)
+    b = build_planar_push(cfg)
+    env = ms.make("robot_planar_push", n, precision="f64", seed=seed, autoreset=True, config=cfg)
+    env.reset()
+    ora = OracleEnvs(b, n)
+    episode = np.ones(n, int)
+    for e in range(n):
+        push_reset_state(b, ora.states[e], seed, e, 1)
+    obs_reset, *_ = ora.finish_reset(150)
+    q, v, _ = _qv(env, 27, 24)
+    d0 = np.abs(q - ora.field("qpos", 27)).max(1)
+    print("device reset (sampling + IK + 150 settle substeps) vs oracle: max|dq|", d0.max(), "p99", np.percentile(d0, 99))
+    assert d0.max() < 1e-6
+    assert np.abs(env._obs.cpu().numpy() - obs_reset).max() < 1e-5
+    rng = np.random.RandomState(seed + 1)
+    nexcl = nterm = ntrunc = 0
+    ok = np.ones(n, bool)  # envs still compared (dropped for good once they come within 1e-6 of a threshold)
+    worst_q = worst_final = worst_reset = 0.0
+    for k in range(steps):
+        qp = ora.field("qpos", 27)
+        a = np.stack([rng.uniform(-0.2, 0.2, n), rng.uniform(-0.6, -0.3, n)], 1)
+        if k % 2 == 0:
+            a = qp[:, 6:8] + rng.uniform(-0.01, 0.01, (n, 2))
+        a = a.astype(np.float32)
+        obs_o, rew_o, _, fl_o = ora.step(a.astype(np.float64))
+        env.step(torch.from_numpy(a).cuda())
+        fl = env._flags.cpu().numpy(); obs = env._obs.cpu().numpy(); fobs = env._final_obs.cpu().numpy()
+        blocks, tgt = obs_o[:, 5:11].reshape(n, 3, 2), obs_o[:, 3:5]
+        close = np.abs(np.linalg.norm(blocks - tgt[:, None], axis=2) - radius).min(1) < 1e-6
+        nexcl += int((ok & close).sum())
+        ok &= ~close
+        np.testing.assert_array_equal(fl[ok], fl_o[ok], err_msg=f"flags differ at step {k}")
+        worst_final = max(worst_final, np.abs(fobs - obs_o)[ok].max())
+        done = fl_o[:, 3].astype(bool)
+        nterm += int(fl_o[ok, 0].sum()); ntrunc += int(fl_o[ok, 1].sum())
+        if done.any():  # the oracle side of the auto-reset
+            idx = np.nonzero(done)[0]
+            tmp = OracleEnvs(b, len(idx))
+            for j, e in enumerate(idx):
+                episode[e] += 1
+                push_reset_state(b, tmp.states[j], seed, int(e), int(episode[e]))
+            o_new, *_ = tmp.finish_reset(150)
+            for j, e in enumerate(idx):
+                ctypes.memmove(ctypes.byref(ora.states[e]), ctypes.byref(tmp.states[j]), ctypes.sizeof(MjsEnvState))
+            worst_reset = max(worst_reset, np.abs(obs[idx] - o_new)[ok[idx]].max())
+            obs_o[idx] = o_new
+        assert np.abs(obs - obs_o)[ok].max() < 1e-3, k
+        q, v, st = _qv(env, 27, 24)
+        worst_q = max(worst_q, np.abs(q - ora.field("qpos", 27))[ok].max())
+        np.testing.assert_array_equal(np.array([s.episode_id for s in st]), episode)
+    print("push autoreset rollout:", steps, "steps x", n, "envs; terminated", nterm, "truncated", ntrunc, "threshold exclusions", nexcl,
+          "max|dq| free-running", worst_q, "max|d final_obs|", worst_final, "max|d obs after reset|", worst_reset)
+    assert nterm > 0 and ntrunc >= n  # every env crossed at least one step-limit boundary; some succeeded
+    assert episode.min() >= 3         # two boundaries each: slot adoption, then inline / job-warp resets
+    assert nexcl < n // 50
+    assert worst_q < 1e-3 and worst_final < 1e-3 and worst_reset < 1e-4
+    env.close()
+
+
+def test_button_f64_scripted_rollout_flags_are_exact_on_1024_envs():
+    """Button Push in f64 at the default tolerance: the scripted demonstrator (robot_push_button.py:231-300) drives 1024
+    envs through approach, press, toggle, retreat to the end pose and termination.  Free-running on both sides with the same
+    float32 actions: pressed / active / success / terminated / truncated identical at every control step, |dq| <= 1e-4
+    throughout.  An env is dropped (and counted) from the step the oracle's touch force comes within 1e-6 N of 5 N or 200 N."""
+    import mujoco_sim_b200 as ms
+    from mujoco_sim_b200.model.tasks import build_push_button
+
+    n, steps, b = 1024, 100, build_push_button()
+    ora = arm_states(b, n, 9)
+    env = ms.make("robot_push_button", n, precision="f64", autoreset=False)
+    env.set_state(copy_states(ora.states, n), forward=True)
+    ok = np.ones(n, bool); alive = np.ones(n, bool)
+    npress = ntoggle = nsucc = nterm = ntrunc = nexcl = 0
+    worst_q = 0.0
+    lo, hi = b.task.touch_lo, b.task.touch_hi
+    prev_active = np.zeros(n, int)
+    for k in range(steps):
+        a, _ = ora.demo_policy()
+        a = a.astype(np.float32)
+        (obs_o, rew_o, _, fl_o), touch = ora.step_touch(a.astype(np.float64))
+        env.step(torch.from_numpy(a).cuda())
+        q, v, st = _qv(env, 6, 6)
+        close = (np.minimum(np.abs(touch - lo), np.abs(touch - hi)).min(1) < 1e-6)
+        nexcl += int((ok & alive & close).sum())
+        ok &= ~close
+        chk = ok & alive
+        swa = np.array([s.sw_active for s in st]); swp = np.array([s.sw_pressed for s in st]); swc = np.array([s.sw_count for s in st])
+        swa_o, swp_o, swc_o = ora.field("sw_active"), ora.field("sw_pressed"), ora.field("sw_count")
+        np.testing.assert_array_equal(swp[chk], swp_o[chk], err_msg=f"pressed differs at step {k}")
+        np.testing.assert_array_equal(swa[chk], swa_o[chk], err_msg=f"active differs at step {k}")
+        np.testing.assert_array_equal(swc[chk], swc_o[chk], err_msg=f"pressed-substep count differs at step {k}")
+        np.testing.assert_array_equal(env._flags.cpu().numpy()[chk], fl_o[chk], err_msg=f"flags differ at step {k}")
+        assert np.abs(env._reward.cpu().numpy() - rew_o)[chk].max() == 0
+        worst_q = max(worst_q, np.abs(q - ora.field("qpos", 6))[chk].max())
+        npress += int(swp_o[chk].sum()); ntoggle += int((swa_o != prev_active)[chk].sum())
+        nsucc += int(fl_o[chk, 2].sum()); nterm += int(fl_o[chk, 0].sum()); ntrunc += int(fl_o[chk, 1].sum())
+        prev_active = swa_o.copy()
+        alive &= ~fl_o[:, 3].astype(bool)
+        if not alive.any():
+            break
+    print("button f64 scripted rollout:", n, "envs,", k + 1, "steps; pressed env-steps", npress, "toggles", ntoggle, "successes", nsucc, "terminated", nterm,
+          "truncated", ntrunc, "threshold exclusions", nexcl, "max|dq| free-running", worst_q)
+    assert npress > n // 2 and ntoggle > n // 2 and nterm > n // 2
+    assert nexcl <= n // 100
+    assert worst_q < TOL_CONTACT_STEP
+    env.close()
