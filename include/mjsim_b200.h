@@ -39,6 +39,18 @@ void mjs_destroy(MjsSim* sim);
  * with Philox keyed by (seed, global env id, episode id).  d_obs may be NULL. */
 int mjs_reset(MjsSim* sim, const unsigned char* d_mask, float* d_obs, void* stream);
 
+/* Replaces: DMCEnvironmentAdapter.seed (dmc2gym.py:126-131), which installs RandomState(seed) on a LIVE env so that the
+ * next reset draws from it (reset(seed=s) calls it first, dmc2gym.py:157-160).  Re-keys the Philox streams, sets every env's
+ * episode counter and the action-stream index back to 0 and discards the next-episode slots prepared under the old key: two
+ * resets after mjs_reseed(sim, s) with the same s produce identical episodes (test/test_gym_envs.py:21-36).  Synchronises. */
+int mjs_reseed(MjsSim* sim, unsigned long long seed);
+
+/* Replaces: the float64 observation / reward arrays the reference returns (dm_env specs are float64: dmc2gym.py:66-75,
+ * reward is a Python float).  Registers caller-owned DEVICE buffers obs64 [N][O], reward64 [N], final_obs64 [N][O] (any may
+ * be NULL; all NULL = off) that every later mjs_reset / mjs_step* fills with the unrounded double values next to the float32
+ * outputs.  The buffers must stay valid until they are replaced or the simulator is destroyed. */
+int mjs_set_output64(MjsSim* sim, double* d_obs64, double* d_reward64, double* d_final_obs64);
+
 /* Replaces: DMCEnvironmentAdapter.step (dmc2gym.py:133-155) for all envs.
  * d_actions [N][A] float32 (NULL: synthetic rollout, actions ~ U(action box)
  * drawn on device), d_obs [N][O], d_reward [N], d_flags [N][4] bytes

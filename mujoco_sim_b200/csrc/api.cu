@@ -27,7 +27,8 @@ struct MjsSim {
   long long launches;
   double* d_stats;
   // host-call staging (pinned host + device)
-  float *d_act, *d_obs, *d_rew, *d_fobs, *h_pin;
+  float *d_act, *d_obs, *d_rew, *d_fobs;
+  double *obs64, *rew64, *fobs64;  // caller-owned float64 outputs registered by mjs_set_output64 (may be null)
   unsigned char *d_flags, *d_mask;
   cudaStream_t hstream;
   // PointMass
@@ -138,9 +139,20 @@ static int build_pm_params(const MjsModel& m, const MjsTask& t, PmParams<real>& 
 static PmIO pm_io(MjsSim* s, const float* act, float* obs, float* rew, unsigned char* flags, float* fobs, int autoreset) {
   PmIO io;
   io.sd = s->pm_sd; io.si = s->pm_si; io.actions = act; io.obs = obs; io.reward = rew; io.flags = flags; io.final_obs = fobs;
+  io.obs64 = s->obs64; io.reward64 = s->rew64; io.final_obs64 = s->fobs64;
   io.stats = s->d_stats; io.N = s->N; io.autoreset = autoreset; io.seed = s->seed; io.env_offset = s->env_offset; io.step_index = s->step_index;
   return io;
 }
+
+// Every entry point runs with the simulator's device current and leaves the caller's current device as it found it
+// (a simulator created on cuda:1 may be stepped while the caller's current device is cuda:0).
+struct DeviceGuard {
+  int prev = -1, changed = 0;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) { cudaSetDevice(dev); changed = 1; }
+  }
+  ~DeviceGuard() { if (changed) cudaSetDevice(prev); }
+};
 
 extern "C" {
 
@@ -159,7 +171,8 @@ int mjs_create(const MjsModel* model, const MjsTask* task, int num_envs, int dev
     mjs_set_error("mjs_create: no CUDA device -- this library has no CPU fallback");
     return -2;
   }
-  MJS_CUDA_CHECK(cudaSetDevice(device));
+  if (device < 0 || device >= ndev) { mjs_set_error("mjs_create: device %d out of range (%d visible)", device, ndev); return -1; }
+  DeviceGuard guard(device);
   MjsSim* s = new MjsSim();
   memset(s, 0, sizeof(*s));
   s->model = *model; s->task = *task; s->N = num_envs; s->device = device; s->seed = seed; s->env_offset = env_offset; s->precision = precision;
@@ -189,16 +202,16 @@ int mjs_create(const MjsModel* model, const MjsTask* task, int num_envs, int dev
 
 void mjs_destroy(MjsSim* s) {
   if (!s) return;
-  cudaSetDevice(s->device);
+  DeviceGuard guard(s->device);
   cudaFree(s->d_stats); cudaFree(s->d_act); cudaFree(s->d_obs); cudaFree(s->d_fobs); cudaFree(s->d_rew); cudaFree(s->d_flags); cudaFree(s->d_mask);
   cudaFree(s->pm_sd); cudaFree(s->pm_si);
-  if (s->h_pin) cudaFreeHost(s->h_pin);
   if (s->arm) arm_destroy(s->arm);
   cudaStreamDestroy(s->hstream);
   delete s;
 }
 
 int mjs_reset(MjsSim* s, const unsigned char* d_mask, float* d_obs, void* stream) {
+  DeviceGuard guard(s->device);
   cudaStream_t st = (cudaStream_t)stream;
   if (s->task.kind == MJS_TASK_POINTMASS) {
     PmIO io = pm_io(s, nullptr, d_obs, nullptr, nullptr, nullptr, 0);
@@ -216,6 +229,7 @@ int mjs_reset(MjsSim* s, const unsigned char* d_mask, float* d_obs, void* stream
 }
 
 int mjs_step(MjsSim* s, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags, float* d_final_obs, int autoreset, void* stream) {
+  DeviceGuard guard(s->device);
   cudaStream_t st = (cudaStream_t)stream;
   if (s->task.kind == MJS_TASK_POINTMASS) {
     PmIO io = pm_io(s, d_actions, d_obs, d_reward, d_flags, d_final_obs, autoreset);
@@ -235,6 +249,7 @@ int mjs_step(MjsSim* s, const float* d_actions, float* d_obs, float* d_reward, u
 }
 
 int mjs_step_noalloc(MjsSim* s, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags, float* d_final_obs, int autoreset, void* stream) {
+  DeviceGuard guard(s->device);
   if (!s->arm) return mjs_step(s, d_actions, d_obs, d_reward, d_flags, d_final_obs, autoreset, stream);  // PointMass: the step uses no scratch and allocates nothing
   int r = arm_step_noalloc(s->arm, d_actions, d_obs, d_reward, d_flags, d_final_obs, autoreset, s->step_index, (cudaStream_t)stream);
   if (r < 0) return r;
@@ -244,15 +259,8 @@ int mjs_step_noalloc(MjsSim* s, const float* d_actions, float* d_obs, float* d_r
   return 0;
 }
 
-static int ensure_pin(MjsSim* s) {
-  if (s->h_pin) return 0;
-  size_t n = (size_t)s->N * (s->task.action_dim + 2 * s->task.obs_dim + 1) * sizeof(float) + 4 * (size_t)s->N + s->N;
-  MJS_CUDA_CHECK(cudaMallocHost(&s->h_pin, n));
-  return 0;
-}
-
 int mjs_step_host(MjsSim* s, const float* h_actions, float* h_obs, float* h_reward, unsigned char* h_flags, float* h_final_obs, int autoreset) {
-  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  DeviceGuard guard(s->device);
   int N = s->N, A = s->task.action_dim, O = s->task.obs_dim;
   cudaStream_t st = s->hstream;
   if (h_actions) MJS_CUDA_CHECK(cudaMemcpyAsync(s->d_act, h_actions, sizeof(float) * N * A, cudaMemcpyHostToDevice, st));
@@ -267,7 +275,7 @@ int mjs_step_host(MjsSim* s, const float* h_actions, float* h_obs, float* h_rewa
 }
 
 int mjs_reset_host(MjsSim* s, const unsigned char* h_mask, float* h_obs) {
-  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  DeviceGuard guard(s->device);
   cudaStream_t st = s->hstream;
   if (h_mask) MJS_CUDA_CHECK(cudaMemcpyAsync(s->d_mask, h_mask, s->N, cudaMemcpyHostToDevice, st));
   int r = mjs_reset(s, h_mask ? s->d_mask : nullptr, s->d_obs, st);
@@ -278,7 +286,7 @@ int mjs_reset_host(MjsSim* s, const unsigned char* h_mask, float* h_obs) {
 }
 
 int mjs_set_state(MjsSim* s, const MjsEnvState* h, int first, int count, int forward) {
-  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  DeviceGuard guard(s->device);
   MJS_CUDA_CHECK(cudaDeviceSynchronize());
   int N = s->N;
   if (first < 0 || count < 0 || first + count > N) { mjs_set_error("mjs_set_state: range out of bounds"); return -1; }
@@ -305,7 +313,7 @@ int mjs_set_state(MjsSim* s, const MjsEnvState* h, int first, int count, int for
 }
 
 int mjs_get_state(MjsSim* s, MjsEnvState* h, int first, int count) {
-  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  DeviceGuard guard(s->device);
   MJS_CUDA_CHECK(cudaDeviceSynchronize());
   int N = s->N;
   if (first < 0 || count < 0 || first + count > N) { mjs_set_error("mjs_get_state: range out of bounds"); return -1; }
@@ -331,24 +339,25 @@ int mjs_get_state(MjsSim* s, MjsEnvState* h, int first, int count) {
 }
 
 int mjs_join_aux(MjsSim* s, void* stream) {
+  DeviceGuard guard(s->device);
   if (!s->arm) return 0;
   return arm_join_aux(s->arm, (cudaStream_t)stream);
 }
 
 int mjs_debug_forward(MjsSim* s, int env, double* h_out, int n) {
   if (!s->arm) { mjs_set_error("mjs_debug_forward: articulated tasks only"); return -1; }
-  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  DeviceGuard guard(s->device);
   return arm_debug_forward(s->arm, env, h_out, n);
 }
 
 int mjs_debug_substeps(MjsSim* s, int k) {
   if (!s->arm) { mjs_set_error("mjs_debug_substeps: articulated tasks only"); return -1; }
-  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  DeviceGuard guard(s->device);
   return arm_debug_substeps(s->arm, k);
 }
 
 int mjs_demo_policy(MjsSim* s, double noise, float* d_actions, int* d_ok, void* stream) {
-  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  DeviceGuard guard(s->device);
   cudaStream_t st = (cudaStream_t)stream;
   if (!d_actions) { mjs_set_error("mjs_demo_policy: d_actions is null"); return -1; }
   if (s->task.kind == MJS_TASK_POINTMASS) {
@@ -368,14 +377,30 @@ int mjs_demo_policy(MjsSim* s, double noise, float* d_actions, int* d_ok, void* 
 
 int mjs_debug_times(MjsSim* s, long long* h_out, int n) {
   if (!s->arm) { mjs_set_error("mjs_debug_times: articulated tasks only"); return -1; }
-  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  DeviceGuard guard(s->device);
   return arm_debug_times(s->arm, h_out, n);
+}
+
+int mjs_set_output64(MjsSim* s, double* d_obs64, double* d_reward64, double* d_final_obs64) {
+  s->obs64 = d_obs64; s->rew64 = d_reward64; s->fobs64 = d_final_obs64;
+  if (s->arm) arm_set_output64(s->arm, d_obs64, d_reward64, d_final_obs64);
+  return 0;
+}
+
+int mjs_reseed(MjsSim* s, unsigned long long seed) {
+  DeviceGuard guard(s->device);
+  s->seed = seed;
+  s->step_index = 0;
+  if (s->arm) return arm_reseed(s->arm, seed);
+  MJS_CUDA_CHECK(cudaDeviceSynchronize());
+  MJS_CUDA_CHECK(cudaMemset(s->pm_si + (size_t)PM_I_EPISODE * s->N, 0, sizeof(int) * (size_t)s->N));
+  return 0;
 }
 
 int mjs_stats_device(MjsSim* s, double** d_out) { *d_out = s->d_stats; return 0; }
 
 int mjs_stats(MjsSim* s, double* h_out8, int reset) {
-  MJS_CUDA_CHECK(cudaSetDevice(s->device));
+  DeviceGuard guard(s->device);
   MJS_CUDA_CHECK(cudaDeviceSynchronize());
   MJS_CUDA_CHECK(cudaMemcpy(h_out8, s->d_stats, 8 * sizeof(double), cudaMemcpyDeviceToHost));
   if (reset) MJS_CUDA_CHECK(cudaMemset(s->d_stats, 0, 8 * sizeof(double)));

@@ -27,7 +27,7 @@ ArmSim* arm_create(const MjsModel& m, const MjsTask& t, int N, unsigned long lon
   if (cudaMalloc(&a->queue, 64) != cudaSuccess) { mjs_set_error("arm engine: cudaMalloc (work queue) failed"); delete a; return nullptr; }
   if (a->mf.settle_steps > 0) {
     if (cudaMalloc(&a->slot_sd, sizeof(double) * (size_t)a->SD * N) != cudaSuccess || cudaMalloc(&a->slot_si, sizeof(int) * (size_t)a->SI * N) != cudaSuccess ||
-        cudaMalloc(&a->slot_obs, sizeof(float) * 16 * (size_t)N) != cudaSuccess || cudaMalloc(&a->slot_ready, sizeof(int) * (size_t)N) != cudaSuccess) {
+        cudaMalloc(&a->slot_obs, sizeof(double) * 16 * (size_t)N) != cudaSuccess || cudaMalloc(&a->slot_ready, sizeof(int) * (size_t)N) != cudaSuccess) {
       mjs_set_error("arm engine: cudaMalloc (reset slots) failed"); delete a; return nullptr;
     }
     cudaMemset(a->slot_sd, 0, sizeof(double) * (size_t)a->SD * N);
@@ -73,6 +73,7 @@ static ArmIO make_io(ArmSim* a) {
   // (profiles/r1/sync_modes.txt, exp9): level 1 for both precisions.
   { const char* lv = getenv("MJS_SYNC_LEVEL"); io.sync_level = lv ? atoi(lv) : 1; }
   io.sd = a->sd; io.si = a->si; io.stats = a->d_stats;
+  io.obs64 = a->obs64; io.reward64 = a->reward64; io.final_obs64 = a->final_obs64;
   io.slot_sd = a->slot_sd; io.slot_si = a->slot_si; io.slot_obs = a->slot_obs; io.slot_ready = a->slot_ready; io.slot_prog = a->slot_prog; io.times = a->d_times; io.N = a->N; io.seed = a->seed; io.env_offset = a->env_offset;
   return io;
 }
@@ -172,6 +173,26 @@ int arm_step_noalloc(ArmSim* a, const float* d_actions, float* d_obs, float* d_r
   io.jobs = base; io.job_cap = a->job_cap;
   io.njobs = counters; io.njobs_next = counters + 1;
   return dispatch(a, 0, io, st);
+}
+
+void arm_set_output64(ArmSim* a, double* d_obs64, double* d_reward64, double* d_final_obs64) {
+  a->obs64 = d_obs64; a->reward64 = d_reward64; a->final_obs64 = d_final_obs64;
+}
+
+// mjs_reseed: new Philox key, episode counters back to 0 (so a reset after reseeding with the same seed repeats the same
+// episodes, dmc2gym.py:126-131,157-163), every pre-settled slot of the old key discarded
+int arm_reseed(ArmSim* a, unsigned long long seed) {
+  MJS_CUDA_CHECK(cudaDeviceSynchronize());
+  a->seed = seed;
+  MJS_CUDA_CHECK(cudaMemset2D(a->si + 6 /* I_EPISODE */, sizeof(int) * a->SI, 0, sizeof(int), a->N));
+  if (a->slot_ready) {
+    MJS_CUDA_CHECK(cudaMemset(a->slot_ready, 0, sizeof(int) * (size_t)a->N));
+    MJS_CUDA_CHECK(cudaMemset(a->slot_prog, 0, sizeof(int) * (size_t)a->N));
+    MJS_CUDA_CHECK(cudaMemset(a->slot_si, 0, sizeof(int) * (size_t)a->SI * a->N));
+    MJS_CUDA_CHECK(cudaMemset(a->jobs, 0, sizeof(int) * ((size_t)a->job_cap + 64 + 2)));
+    a->refill_pending = 0;
+  }
+  return 0;
 }
 
 // make `st` wait for the refill work in flight (bench: close the timed region)

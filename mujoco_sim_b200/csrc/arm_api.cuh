@@ -17,3 +17,5 @@ int arm_debug_times(ArmSim* a, long long* h_out, int n);
 int arm_demo_policy(ArmSim* a, double noise, unsigned int step_index, float* d_actions, int* d_ok, cudaStream_t st);
 int arm_step_noalloc(ArmSim* a, const float* d_actions, float* d_obs, float* d_reward, unsigned char* d_flags, float* d_final_obs, int autoreset,
                      unsigned int step_index, cudaStream_t st);
+void arm_set_output64(ArmSim* a, double* d_obs64, double* d_reward64, double* d_final_obs64);
+int arm_reseed(ArmSim* a, unsigned long long seed);

@@ -1635,6 +1635,7 @@ struct ArmIO {
   float* reward;
   unsigned char* flags;
   float* final_obs;
+  double *obs64, *reward64, *final_obs64;  // optional float64 twins of obs / reward / final_obs (mjs_set_output64; the reference emits float64, dmc2gym.py:66-75)
   double* stats;
   const unsigned char* mask;
   int N, autoreset;
@@ -1644,7 +1645,7 @@ struct ArmIO {
   // pre-settled next-episode states (tasks with settle steps): see arm_reset_kernel
   double* slot_sd;
   int* slot_si;
-  float* slot_obs;
+  double* slot_obs;
   int* slot_ready;
   // settle jobs folded into the step kernel's grid (arm_jobs_kernel + the job blocks of arm_step_kernel)
   int* slot_prog;   // settle substeps already done for the slot under preparation (0: not started)
@@ -1972,11 +1973,12 @@ template <typename real, int NOBJ>
 __device__ __forceinline__ void arm_write_out(const ArmModel<real>& A, const ArmIO& io, int e, int lane,
                                               const typename ArmTask<real, NOBJ>::Out& o, bool write_flags) {
   int O = A.obs_dim;
-  if (io.obs && lane < O) {
+  if ((io.obs || io.obs64) && lane < O) {
     double v = 0;
 #pragma unroll
     for (int k = 0; k < 16; k++) if (k == lane) v = o.obs[k];
-    io.obs[(size_t)e * O + lane] = (float)v;
+    if (io.obs) io.obs[(size_t)e * O + lane] = (float)v;
+    if (io.obs64) io.obs64[(size_t)e * O + lane] = v;
   }
   if (write_flags && lane == 0) {
     if (io.reward) io.reward[e] = (float)o.reward;
@@ -2039,7 +2041,7 @@ __device__ __noinline__ void arm_settle_job(const ArmModel<real>& A, WarpMem<rea
       double v = 0;
 #pragma unroll
       for (int k = 0; k < 16; k++) if (k == lane) v = o.obs[k];
-      io.slot_obs[(size_t)e * 16 + lane] = (float)v;
+      io.slot_obs[(size_t)e * 16 + lane] = v;
     }
   }
   T.status = 0;
@@ -2094,14 +2096,16 @@ __device__ __noinline__ void arm_step_env(const ArmModel<real>& A, WarpMem<real,
   __syncwarp();
   if (lane == 0) W.sync = 0;  // an inline reset below runs on its own: no further block barriers
   __syncwarp();
-  if (io.final_obs && lane < A.obs_dim) {
+  if ((io.final_obs || io.final_obs64) && lane < A.obs_dim) {
     double v = 0;
 #pragma unroll
     for (int k = 0; k < 16; k++) if (k == lane) v = o.obs[k];
-    io.final_obs[(size_t)e * A.obs_dim + lane] = (float)v;
+    if (io.final_obs) io.final_obs[(size_t)e * A.obs_dim + lane] = (float)v;
+    if (io.final_obs64) io.final_obs64[(size_t)e * A.obs_dim + lane] = v;
   }
   if (lane == 0) {
     if (io.reward) io.reward[e] = (float)o.reward;
+    if (io.reward64) io.reward64[e] = o.reward;
     if (io.flags) reinterpret_cast<uchar4*>(io.flags)[e] = make_uchar4(o.terminated, o.truncated, o.success, o.done);
     if (io.stats) {  // solver effort: env-substeps and Newton iterations (mjs_stats slots 6 and 7)
       atomicAdd(io.stats + 6, (double)A.n_sub); atomicAdd(io.stats + 7, (double)o.nit_sum);
@@ -2137,7 +2141,13 @@ __device__ __noinline__ void arm_step_env(const ArmModel<real>& A, WarpMem<real,
         double* dst = io.sd + (size_t)e * L::SD;
         for (int k = lane; k < L::SD; k += 32) dst[k] = src[k];
         if (lane < L::SI) io.si[(size_t)e * L::SI + lane] = io.slot_si[(size_t)e * L::SI + lane];
-        if (io.obs && lane < A.obs_dim) io.obs[(size_t)e * A.obs_dim + lane] = io.slot_obs[(size_t)e * 16 + lane];
+        if (lane < A.obs_dim) {
+          const double v = io.slot_obs[(size_t)e * 16 + lane];
+          if (io.obs) io.obs[(size_t)e * A.obs_dim + lane] = (float)v;
+          if (io.obs64) io.obs64[(size_t)e * A.obs_dim + lane] = v;
+        }
+        // the status word is sticky across episodes on the inline-reset path (T.status survives reset_begin): same here
+        if (lane == 0 && (T.status | W.status)) io.si[(size_t)e * L::SI + L::I_STATUS] |= T.status | W.status;
         __syncwarp();
         if (lane == 0) { __threadfence(); *((volatile int*)(io.slot_ready + e)) = 0; }
         took = true;
@@ -2226,7 +2236,7 @@ __global__ void __launch_bounds__(WPB * 32) arm_reset_kernel(ArmIO io, int refil
       double v = 0;
 #pragma unroll
       for (int k = 0; k < 16; k++) if (k == lane) v = o.obs[k];
-      io.slot_obs[(size_t)e * 16 + lane] = (float)v;
+      io.slot_obs[(size_t)e * 16 + lane] = v;
     }
     __syncwarp();
     if (lane == 0) { io.slot_prog[e] = 0; __threadfence(); *((volatile int*)(io.slot_ready + e)) = 1; }

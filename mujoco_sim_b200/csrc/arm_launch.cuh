@@ -43,10 +43,12 @@ static int launch(ArmSim* a, const ArmModel<real>& M, int which, ArmIO io, cudaS
     }
     int blocks = (n + WPBS - 1) / WPBS + io.job_blocks;
     if (io.queue) {  // persistent grid: as many blocks as are resident at once (one per SM: shared memory is full)
-      static int resident = 0;
+      static int resident_of[64];  // per device (this function is one template instantiation = one kernel)
+      int dev = 0;
+      MJS_CUDA_CHECK(cudaGetDevice(&dev));
+      int& resident = resident_of[dev & 63];
       if (!resident) {
-        int dev = 0, sms = 0, per_sm = 0;
-        MJS_CUDA_CHECK(cudaGetDevice(&dev));
+        int sms = 0, per_sm = 0;
         MJS_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
         MJS_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, WPBS * 32, smem_step));
         resident = sms * (per_sm > 0 ? per_sm : 1);

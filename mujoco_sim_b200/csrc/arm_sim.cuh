@@ -35,7 +35,8 @@ struct ArmSim {
   // pre-settled reset slots + side stream (tasks with settle steps)
   double* slot_sd;
   int* slot_si;
-  float* slot_obs;
+  double* slot_obs;
+  double *obs64, *reward64, *final_obs64;  // registered by mjs_set_output64 (may be null)
   int* slot_ready;
   int* slot_prog;
   int* jobs;      // job_cap env ids + the two ping-pong counters behind them

@@ -169,6 +169,7 @@ struct PmIO {
   float* reward;       // [N]
   unsigned char* flags;  // [N][4]
   float* final_obs;    // [N][4] observation of the terminal state (before auto-reset), may be null
+  double *obs64, *reward64, *final_obs64;  // optional float64 twins (mjs_set_output64), may be null
   double* stats;       // [8] accumulators: return sum, length sum, episodes, successes, truncations, errors, env-steps
   int N, autoreset;
   unsigned long long seed;
@@ -240,6 +241,7 @@ __global__ void __launch_bounds__(128) pm_reset_kernel(PmParams<real> P, PmIO io
     float4 o = make_float4((float)((double)P.body_x + qx), (float)((double)P.body_y + qy), (float)tx, (float)ty);
     reinterpret_cast<float4*>(io.obs)[e] = o;
   }
+  if (io.obs64) { double* o = io.obs64 + 4 * (size_t)e; o[0] = (double)P.body_x + qx; o[1] = (double)P.body_y + qy; o[2] = tx; o[3] = ty; }
 }
 
 template <typename real>
@@ -296,8 +298,11 @@ __global__ void __launch_bounds__(128) pm_step_kernel(PmParams<real> P, PmIO io)
     float4 o = make_float4((float)px, (float)py, (float)tx, (float)ty);
     uchar4 f = make_uchar4(last && goal, last && !goal, goal, last);
     io.reward[e] = (float)reward;
+    if (io.reward64) io.reward64[e] = reward;
     reinterpret_cast<uchar4*>(io.flags)[e] = f;
     if (io.final_obs) reinterpret_cast<float4*>(io.final_obs)[e] = o;
+    if (io.final_obs64) { double* d = io.final_obs64 + 4 * (size_t)e; d[0] = px; d[1] = py; d[2] = tx; d[3] = ty; }
+    double o64[4] = {px, py, tx, ty};
     int episode = io.si[PM_I_EPISODE * N + e];
     int status = io.si[PM_I_STATUS * N + e] | (bad ? MJS_STATUS_NAN : 0);
     if (last) {
@@ -309,8 +314,10 @@ __global__ void __launch_bounds__(128) pm_step_kernel(PmParams<real> P, PmIO io)
       mx = qx; my = qy; vx = 0; vy = 0; time = 0; ret = 0; steps = 0;
       pm_forward_reset<real>(P, (real)qx, (real)qy, (real)mx, (real)my, wx, wy);
       o = make_float4((float)((double)P.body_x + qx), (float)((double)P.body_y + qy), (float)tx, (float)ty);
+      o64[0] = (double)P.body_x + qx; o64[1] = (double)P.body_y + qy; o64[2] = tx; o64[3] = ty;
     }
     reinterpret_cast<float4*>(io.obs)[e] = o;
+    if (io.obs64) { double* d = io.obs64 + 4 * (size_t)e; d[0] = o64[0]; d[1] = o64[1]; d[2] = o64[2]; d[3] = o64[3]; }
     s[PM_QX * N + e] = qx; s[PM_QY * N + e] = qy; s[PM_VX * N + e] = vx; s[PM_VY * N + e] = vy;
     s[PM_MX * N + e] = mx; s[PM_MY * N + e] = my; s[PM_WX * N + e] = (double)wx; s[PM_WY * N + e] = (double)wy;
     s[PM_TIME * N + e] = time; s[PM_TX * N + e] = tx; s[PM_TY * N + e] = ty;

@@ -38,7 +38,8 @@ def _ptr(t: Optional[torch.Tensor]):
 
 class BatchedMujocoSimEnv:
     def __init__(self, task_name: str, num_envs: int, device="cuda:0", seed: int = 0, env_offset: int = 0,
-                 precision: str = "f64", autoreset: bool = True, solver_tolerance: Optional[float] = None, **task_kwargs):
+                 precision: str = "f64", autoreset: bool = True, solver_tolerance: Optional[float] = None, obs_dtype: str = "float32",
+                 **task_kwargs):
         if not torch.cuda.is_available():
             raise _lib.MjsimError("BatchedMujocoSimEnv needs a CUDA device (there is no CPU fallback)")
         self.bundle = _BUILDERS[task_name](**task_kwargs)
@@ -63,6 +64,17 @@ class BatchedMujocoSimEnv:
         self._final_obs = torch.zeros(N, O, dtype=torch.float32, **kw)
         self._reward = torch.zeros(N, dtype=torch.float32, **kw)
         self._flags = torch.zeros(N, 4, dtype=torch.uint8, **kw)
+        # float64 observations / rewards like the reference's (dm_env specs are float64, dmc2gym.py:66-75): the kernels
+        # write the unrounded doubles into these tensors next to the float32 ones (mjs_set_output64)
+        assert obs_dtype in ("float32", "float64"), obs_dtype
+        self.obs_dtype = obs_dtype
+        self._obs64 = self._final_obs64 = self._reward64 = None
+        if obs_dtype == "float64":
+            self._obs64 = torch.zeros(N, O, dtype=torch.float64, **kw)
+            self._final_obs64 = torch.zeros(N, O, dtype=torch.float64, **kw)
+            self._reward64 = torch.zeros(N, dtype=torch.float64, **kw)
+            _lib.check(self._L.mjs_set_output64(self._h, _ptr(self._obs64), _ptr(self._reward64), _ptr(self._final_obs64)))
+        self.seed_value = int(seed)
         self.obs_keys = list(self.bundle.obs_keys)
         self.has_success = task_name in ("point_mass_reach", "robot_push_button")
         self.single_action_low = self.bundle.action_low
@@ -93,13 +105,32 @@ class BatchedMujocoSimEnv:
     # ---------------------------------------------------------------------- API
     def reset(self, seed: Optional[int] = None, env_mask: Optional[torch.Tensor] = None):
         """dmc2gym.py:157-163 for every env (or the masked ones)."""
-        if seed is not None:
-            raise NotImplementedError("re-seeding after construction: create a new env with seed=")
+        if seed is not None:  # dmc2gym.py:157-160: reset(seed=s) re-seeds the live env first
+            self.seed(seed)
         mask = None
         if env_mask is not None:
             mask = env_mask.to(device=self.device, dtype=torch.uint8).contiguous()
         _lib.check(self._L.mjs_reset(self._h, _ptr(mask), _ptr(self._obs), self._stream()))
-        return self._obs_dict(self._obs), {}
+        return self._obs_dict(self.observation), {}
+
+    def seed(self, seed: int):
+        """dmc2gym.py:126-131: install a new random stream on the live env; applied by the next reset.  Episode counters
+        restart, so `reset(seed=s)` twice gives identical episodes (test/test_gym_envs.py:21-36)."""
+        self.seed_value = int(seed)
+        _lib.check(self._L.mjs_reseed(self._h, int(seed) & (2**64 - 1)))
+
+    # the tensors step()/reset() hand out, in the configured dtype
+    @property
+    def observation(self):
+        return self._obs64 if self._obs64 is not None else self._obs
+
+    @property
+    def final_observation(self):
+        return self._final_obs64 if self._final_obs64 is not None else self._final_obs
+
+    @property
+    def reward(self):
+        return self._reward64 if self._reward64 is not None else self._reward
 
     def step(self, actions: Optional[torch.Tensor]):
         """dmc2gym.py:133-155 for every env.  actions=None -> synthetic random rollout."""
@@ -114,9 +145,9 @@ class BatchedMujocoSimEnv:
         if self.has_success:
             info["is_success"] = f[:, 2].float()
         if self.autoreset:
-            info["final_observation"] = self._obs_dict(self._final_obs)
+            info["final_observation"] = self._obs_dict(self.final_observation)
             info["_final_observation"] = f[:, 3].bool()
-        return self._obs_dict(self._obs), self._reward, f[:, 0].bool(), f[:, 1].bool(), info
+        return self._obs_dict(self.observation), self.reward, f[:, 0].bool(), f[:, 1].bool(), info
 
     def step_flat(self, actions):
         """step() without dict assembly: (obs[N,O], reward[N], flags[N,4] u8)."""
@@ -125,7 +156,7 @@ class BatchedMujocoSimEnv:
             a = actions
         _lib.check(self._L.mjs_step(self._h, _ptr(a), _ptr(self._obs), _ptr(self._reward), _ptr(self._flags), _ptr(self._final_obs),
                                     int(self.autoreset), self._stream()))
-        return self._obs, self._reward, self._flags
+        return self.observation, self.reward, self._flags
 
     def step_host(self, actions: np.ndarray, obs: np.ndarray, reward: np.ndarray, flags: np.ndarray):
         """End-to-end call with HOST numpy buffers (H2D + step + D2H inside the library)."""

@@ -56,12 +56,14 @@ def single_action_space(env: BatchedMujocoSimEnv):
 
 
 def single_observation_space(env: BatchedMujocoSimEnv, flatten: bool = False):
-    """dmc2gym.py:93-101 -- Dict of unbounded Boxes per observable (float64 in the reference; this
-    library emits float32), or one flat float32 Box when flatten_observation_space=True."""
+    """dmc2gym.py:93-101 -- Dict of unbounded Boxes per observable in the spec dtype (float64 in the reference: make the
+    env with obs_dtype="float64"; the default here is float32), or one flat float32 Box when flatten_observation_space=True
+    (dmc2gym.py:66-75 casts the flattened observation to float32)."""
     if flatten:
         n = sum(d for _, d in env.obs_keys)
         return _box(np.full(n, -np.inf), np.full(n, np.inf), np.float32)
-    spaces = {k: _box(np.full(d, -np.inf), np.full(d, np.inf), np.float32) for k, d in env.obs_keys}
+    dt = np.float64 if getattr(env, "obs_dtype", "float32") == "float64" else np.float32
+    spaces = {k: _box(np.full(d, -np.inf), np.full(d, np.inf), dt) for k, d in env.obs_keys}
     try:
         import gymnasium
 
@@ -77,6 +79,22 @@ class _HostBuffers:
         self.final = np.zeros((n, o), np.float32)
         self.rew = np.zeros(n, np.float32)
         self.flags = np.zeros((n, 4), np.uint8)
+
+    def step(self, env, actions):
+        """one control step with host buffers: mjs_step_host (float32), or the device call + copies of the float64 tensors"""
+        import ctypes
+
+        from . import lib as _lib
+
+        if env.obs_dtype == "float64":
+            import torch
+
+            env.step_flat(torch.from_numpy(actions).to(env.device))
+            self.obs, self.final = env.observation.cpu().numpy(), env.final_observation.cpu().numpy()
+            self.rew, self.flags = env.reward.cpu().numpy(), env._flags.cpu().numpy()
+            return
+        p = lambda x: x.ctypes.data_as(ctypes.c_void_p)
+        _lib.check(env._L.mjs_step_host(env._h, p(actions), p(self.obs), p(self.rew), p(self.flags), p(self.final), 1))
 
     def split(self, env, flat):
         out, k = {}, 0
@@ -105,8 +123,8 @@ class SB3VecEnvFacade:
         return flat.copy() if self.flatten else self._b.split(self.env, flat)
 
     def reset(self):
-        obs, _ = self.env.reset()
-        self._b.obs[:] = self.env._obs.cpu().numpy()
+        self.env.reset()
+        self._b.obs = self.env.observation.cpu().numpy()
         return self._obs(self._b.obs)
 
     def step_async(self, actions):
@@ -114,24 +132,32 @@ class SB3VecEnvFacade:
 
     def step_wait(self):
         b, e = self._b, self.env
-        from . import lib as _lib
-        import ctypes
-
-        p = lambda x: x.ctypes.data_as(ctypes.c_void_p)
-        _lib.check(e._L.mjs_step_host(e._h, p(self._actions), p(b.obs), p(b.rew), p(b.flags), p(b.final), 1))
+        b.step(e, self._actions)
         f = b.flags
         dones = f[:, 3].astype(bool)
-        infos = []
-        for i in range(self.num_envs):
-            info = {"discount": 0.0 if f[i, 0] else 1.0}
-            if e.has_success:
-                info["is_success"] = float(f[i, 2])
-            if dones[i]:
-                t = b.final[i : i + 1]
-                info["terminal_observation"] = t[0].copy() if self.flatten else {k: v[0] for k, v in b.split(e, t).items()}
-                info["TimeLimit.truncated"] = bool(f[i, 1]) and not bool(f[i, 0])
-            infos.append(info)
+        # One dict per env is the VecEnv protocol, but building 42 k dicts per step would dominate a rollout: envs that are not
+        # done share one of four read-only info dicts (copy before mutating, as VecMonitor does); done envs get their own.
+        code = (f[:, 0] != 0).astype(np.int64) + 2 * (f[:, 2] != 0).astype(np.int64)
+        shared = self._shared_infos
+        infos = [shared[c] for c in code.tolist()]
+        for i in np.nonzero(dones)[0].tolist():
+            info = dict(shared[code[i]])
+            t = b.final[i : i + 1]
+            info["terminal_observation"] = t[0].copy() if self.flatten else {k: v[0] for k, v in b.split(e, t).items()}
+            info["TimeLimit.truncated"] = bool(f[i, 1]) and not bool(f[i, 0])
+            infos[i] = info
         return self._obs(b.obs), b.rew.copy(), dones, infos
+
+    @property
+    def _shared_infos(self):
+        if not hasattr(self, "_shared"):
+            self._shared = []
+            for c in range(4):
+                info = {"discount": 0.0 if c & 1 else 1.0}
+                if self.env.has_success:
+                    info["is_success"] = float(bool(c & 2))
+                self._shared.append(info)
+        return self._shared
 
     def step(self, actions):
         self.step_async(actions)
@@ -154,7 +180,12 @@ class SB3VecEnvFacade:
         return [False] * len(self._indices(indices))
 
     def seed(self, seed=None):
-        return [None] * self.num_envs  # seeding is fixed at construction (Philox keyed by seed, env id, episode)
+        """VecEnv.seed: re-seed the live simulator (DMCEnvironmentAdapter.seed, dmc2gym.py:126-131); applied by the next
+        reset().  Sub-env i draws from the Philox stream keyed by (seed, i), reported SB3-style as seed + i."""
+        if seed is None:
+            seed = int(np.random.randint(0, 2**31 - 1))
+        self.env.seed(seed)
+        return [seed + i for i in range(self.num_envs)]
 
     def _indices(self, indices):
         return range(self.num_envs) if indices is None else ([indices] if isinstance(indices, int) else list(indices))
@@ -177,21 +208,14 @@ class GymnasiumVectorFacade:
         return flat.copy() if self.flatten else self._b.split(self.env, flat)
 
     def reset(self, *, seed=None, options=None):
-        if seed is not None:
-            raise NotImplementedError("pass seed= to make(); re-seeding an existing simulator is not supported")
-        self.env.reset()
-        self._b.obs[:] = self.env._obs.cpu().numpy()
+        self.env.reset(seed=seed)  # dmc2gym.py:157-160: a seed re-seeds the live env before the reset
+        self._b.obs = self.env.observation.cpu().numpy()
         return self._obs(self._b.obs), {}
 
     def step(self, actions):
-        import ctypes
-
-        from . import lib as _lib
-
         b, e = self._b, self.env
         a = np.ascontiguousarray(actions, np.float32).reshape(self.num_envs, e.action_dim)
-        p = lambda x: x.ctypes.data_as(ctypes.c_void_p)
-        _lib.check(e._L.mjs_step_host(e._h, p(a), p(b.obs), p(b.rew), p(b.flags), p(b.final), 1))
+        b.step(e, a)
         f = b.flags
         info = {"discount": 1.0 - f[:, 0].astype(np.float32), "_final_observation": f[:, 3].astype(bool),
                 "final_observation": self._obs(b.final)}
