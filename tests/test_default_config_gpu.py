@@ -21,15 +21,50 @@ def _qv(env, nq, nv):
     return np.array([list(s.qpos)[:nq] for s in st]), np.array([list(s.qvel)[:nv] for s in st]), st
 
 
+def _substep_chain(bundle_full, pre_state, action):
+    """Replay one control step of one env with n_sub = 1..20 on both sides.  Returns (worst |dq|, worst |dv| of
+    oracle(K_i) vs K_{i+1} over the substeps, largest |dv| of oracle(K_i) vs oracle(O_i))."""
+    import mujoco_sim_b200 as ms
+    from mujoco_sim_b200.model.cstruct import MjsEnvState
+    from mujoco_sim_b200.model.tasks import build_planar_push
+    from oracle.oracle import OracleEnvs, lib as olib
+
+    def vec(st):
+        return np.array(list(st.qpos)[:27]), np.array(list(st.qvel)[:24])
+
+    wq = wv = jump = 0.0
+    prev_k = None
+    for ns in range(1, bundle_full.task.n_sub + 1):
+        bb = build_planar_push(); bb.task.n_sub = ns
+        ms.envs.register_builder("_chain", lambda bb=bb: bb)
+        ee = ms.BatchedMujocoSimEnv("_chain", 1, precision="f64", autoreset=False)
+        oo = OracleEnvs(bb, 1)
+        ctypes.memmove(oo.states, ctypes.byref(pre_state), ctypes.sizeof(MjsEnvState))
+        ee.set_state(copy_states(oo.states, 1), forward=False)
+        oo.step(action.astype(np.float64)); ee.step(torch.from_numpy(action).cuda())
+        ks = copy_states(ee.get_state(), 1)
+        ee.close()
+        if prev_k is not None:
+            A = OracleEnvs(bundle_full, 1)
+            ctypes.memmove(A.states, prev_k, ctypes.sizeof(prev_k))
+            olib().oracle_substeps(ctypes.byref(bundle_full.model), ctypes.byref(bundle_full.task), A.states, 1, 1, ctypes.c_double(1e-4))
+            (qa, va), (qk, vk), (qo, vo) = vec(A.states[0]), vec(ks[0]), vec(oo.states[0])
+            wq, wv, jump = max(wq, np.abs(qa - qk).max()), max(wv, np.abs(va - vk).max()), max(jump, np.abs(va - vo).max())
+        prev_k = ks
+    return wq, wv, jump
+
+
 def test_push_default_tolerance_single_step_gate_on_4096_struck_env_steps():
     """Single-step error from identical states <= 1e-4 with the CUDA solver at MuJoCo's default tolerance 1e-8 (the setting
     of the timed run) against the oracle's 1e-12 minimiser; the pusher is driven into a prop on every step.
 
-    Soft contacts switch on discontinuously (a contact that appears at dist = 0 with approach velocity v carries the damping
-    force D b v at once), so a step in which a contact's distance crosses zero within the two sides' rounding difference is
-    amplified by ~1e5: measured on B200, 2 of 12 288 env-steps (probe: tools/gpu_tol_probe2.py; the same two appear with the
-    CUDA solver at 1e-12, so the tolerance is not the cause).  The oracle shows the same sensitivity against itself when its
-    input state is perturbed by 1e-9 (counted below).  Gate: every env-step within 1e-4 except at most 0.05 % such events."""
+    Soft contacts switch on discontinuously (a contact that appears with approach velocity v carries the damping force
+    D b v at once), so the one-substep map of the reference algorithm has jumps: when a contact's onset falls on different
+    substeps for two states 1e-9 apart, the velocities differ by O(h * a) ~ 0.25 afterwards.  Measured on B200: 2 to 5 of
+    12 288 env-steps (profiles/r2/contact_onset_events.txt).  For every such env-step the test replays the control step
+    substep by substep and checks that the kernel follows the ORACLE'S map from the kernel's own state at every substep
+    (oracle(K_i) == K_{i+1}): the implementations agree on identical inputs, the difference is the map's jump.
+    Gate: every env-step within 1e-4, except at most 0.05 % contact-onset events, each verified substep by substep."""
     import mujoco_sim_b200 as ms
     from mujoco_sim_b200.model.tasks import build_planar_push
     from oracle.oracle import OracleEnvs
@@ -40,8 +75,9 @@ def test_push_default_tolerance_single_step_gate_on_4096_struck_env_steps():
     env = ms.make("robot_planar_push", n, precision="f64", autoreset=False)  # solver_tolerance left at the model default
     assert abs(b.model.tolerance - 1e-8) < 1e-20
     rng = np.random.RandomState(42)
-    dq, dr, moved, dself = [], [], [], []
+    dq, dr, moved, dself, events = [], [], [], [], []
     for k in range(steps):
+        pre_states = copy_states(ora.states, n)
         env.set_state(copy_states(ora.states, n), forward=False)
         ctypes.memmove(pert.states, ora.states, ctypes.sizeof(ora.states))
         for e in range(n):  # the oracle against itself from a state perturbed by 1e-9 (props' positions)
@@ -59,6 +95,8 @@ def test_push_default_tolerance_single_step_gate_on_4096_struck_env_steps():
         dq.append(np.abs(q - qo).max(1)); dr.append(np.abs(rew.cpu().numpy() - rew_o)); dself.append(np.abs(pert.field("qpos", 27) - qo).max(1))
         moved.append(np.abs(qo[:, 6:] - before).max(1) > 1e-4)
         np.testing.assert_array_equal(env._flags.cpu().numpy(), fl_o)
+        for e in np.nonzero(dq[-1] > TOL_CONTACT_STEP)[0]:
+            events.append((k, int(e), copy_states(pre_states, n)[e], a[e:e + 1].copy()))
     dq, dr, moved, dself = np.concatenate(dq), np.concatenate(dr), np.concatenate(moved), np.concatenate(dself)
     out = dq > TOL_CONTACT_STEP
     print("push f64, CUDA tol 1e-8 vs oracle 1e-12: env-steps", dq.size, "struck", int(moved.sum()), "p50 %.1e p99 %.1e p99.9 %.1e max %.1e" %
@@ -66,6 +104,11 @@ def test_push_default_tolerance_single_step_gate_on_4096_struck_env_steps():
           "| oracle vs itself perturbed by 1e-9: over 1e-4:", int((dself > TOL_CONTACT_STEP).sum()), "max %.1e" % dself.max(), "| max|dreward| %.1e" % dr.max())
     assert moved.sum() >= 4096
     assert out.sum() <= dq.size // 2000 and moved[out].all()   # rare contact-onset events, struck props only
+    for (kk, e, pre_state, act) in [ev for ev in events if out[ev[0] * n + ev[1]]]:
+        wq, wv, jump = _substep_chain(b, pre_state, act)
+        print("  contact-onset event: step", kk, "env", e, "| kernel vs oracle map on identical states, worst substep: |dq| %.1e |dv| %.1e" % (wq, wv),
+              "| oracle map on the two sides' states differs by |dv| %.1e" % jump)
+        assert wq < 1e-6 and wv < 1e-4 and jump > 1e-3
     assert np.percentile(dq, 99.9) < TOL_CONTACT_STEP * 1e-2 and dq[~out].max() < TOL_CONTACT_STEP and dr.max() < TOL_CONTACT_STEP
     env.close()
 
