@@ -40,10 +40,17 @@ struct PmParams {
   real spawn_lo[2], spawn_hi[2], target_lo[2], target_hi[2], action_lo[2], action_hi[2];
 };
 
+// Constraint rows of one env, sized for what the scene can activate: the 2 weld rows and the pyramids of at most PM_MAXACT
+// planes at once (a sphere in the convex arena touches at most two walls; the ground plane is exactly tangent, dist == 0, and
+// mj_collision drops dist >= margin).  Every array is indexed with compile-time constants (unrolled slot loops with
+// `s < nact` guards), so the rows, their residuals and the line-search scratch live in registers: the previous layout
+// (J[34][2] + D[34] + aref[34] + jar[34] + jd[34] per thread) sat in local memory -- 2.9 M local loads per launch (ncu, r1).
+#define PM_MAXACT 2
 template <typename real>
 struct PmRows {
-  real J[PM_MAXROW][2], D[PM_MAXROW], aref[PM_MAXROW];
-  int n, neq;
+  real wD[2], waref[2];                                           // weld rows: J = -e_i
+  real pD[PM_MAXACT], pJ[PM_MAXACT][4][2], paref[PM_MAXACT][4];  // active planes, in plane order
+  int nact, overflow;
 };
 
 // rows from (q, v, mocap): mj_makeConstraint + mj_makeImpedance + mj_referenceConstraint
@@ -57,43 +64,69 @@ __device__ __forceinline__ void pm_build_rows(const PmParams<real>& P, real qx, 
   for (int i = 0; i < 2; i++) {
     real imp = mjs_impedance<real>(P.weld_solimp, res[i], (real)0);
     real Rr = fmax((real)MJS_MINVAL, (1 - imp) * P.weld_diag / imp);
-    R.J[i][0] = i == 0 ? (real)-1 : (real)0;
-    R.J[i][1] = i == 1 ? (real)-1 : (real)0;
-    R.D[i] = 1 / Rr;
+    R.wD[i] = 1 / Rr;
     real vel = i == 0 ? -vx : -vy;
-    R.aref[i] = -b * vel - k * imp * res[i];
+    R.waref[i] = -b * vel - k * imp * res[i];
   }
-  R.n = 2;
-  R.neq = 2;
+  R.nact = 0; R.overflow = 0;
+#pragma unroll
+  for (int s = 0; s < PM_MAXACT; s++) {
+    R.pD[s] = 0;
+#pragma unroll
+    for (int e = 0; e < 4; e++) { R.pJ[s][e][0] = 0; R.pJ[s][e][1] = 0; R.paref[s][e] = 0; }
+  }
   for (int p = 0; p < P.nplane; p++) {
     real dist = P.pl_nx[p] * (P.body_x + qx) + P.pl_ny[p] * (P.body_y + qy) + P.pl_c0[p];
     // narrowphase keeps dist <= margin; mj_collision excludes dist >= margin - gap (gap = 0)
     if (dist >= P.pl_margin[p]) continue;
+    if (R.nact >= PM_MAXACT) { R.overflow = 1; continue; }
     mjs_kb<real>(P.pl_solref[p], P.pl_solimp[p], P.timestep, &k, &b);
     real imp = mjs_impedance<real>(P.pl_solimp[p], dist, P.pl_margin[p]);
     real R0 = fmax((real)MJS_MINVAL, (1 - imp) * P.pl_diag[p] / imp);
     real mu = P.pl_mu[p] / sqrt(P.impratio);
     real D = 1 / (2 * mu * mu * R0);
+    const int slot = R.nact++;
 #pragma unroll
-    for (int e = 0; e < 4; e++) {
-      int r = R.n++;
-      R.J[r][0] = P.pl_J[p][e][0];
-      R.J[r][1] = P.pl_J[p][e][1];
-      R.D[r] = D;
-      real vel = R.J[r][0] * vx + R.J[r][1] * vy;
-      R.aref[r] = -b * vel - k * imp * (dist - P.pl_margin[p]);
+    for (int s = 0; s < PM_MAXACT; s++) {
+      if (s == slot) {
+        R.pD[s] = D;
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          real j0 = P.pl_J[p][e][0], j1 = P.pl_J[p][e][1];
+          R.pJ[s][e][0] = j0; R.pJ[s][e][1] = j1;
+          R.paref[s][e] = -b * (j0 * vx + j1 * vy) - k * imp * (dist - P.pl_margin[p]);
+        }
+      }
     }
   }
+}
+
+// residuals jar = J a - aref of all rows
+template <typename real>
+struct PmJar { real w[2], p[PM_MAXACT][4]; };
+
+template <typename real>
+__device__ __forceinline__ void pm_jar(const PmRows<real>& R, real ax, real ay, PmJar<real>& j) {
+  j.w[0] = -ax - R.waref[0]; j.w[1] = -ay - R.waref[1];
+#pragma unroll
+  for (int s = 0; s < PM_MAXACT; s++)
+#pragma unroll
+    for (int e = 0; e < 4; e++) j.p[s][e] = R.pJ[s][e][0] * ax + R.pJ[s][e][1] * ay - R.paref[s][e];
 }
 
 template <typename real>
 __device__ __forceinline__ real pm_cost(const PmParams<real>& P, const PmRows<real>& R, real ax, real ay) {
   // qacc_smooth = 0 (no smooth forces act on the two slide dofs)
   real c = (real)0.5 * (P.m00 * ax * ax + 2 * P.m01 * ax * ay + P.m11 * ay * ay);
-  for (int r = 0; r < R.n; r++) {
-    real jar = R.J[r][0] * ax + R.J[r][1] * ay - R.aref[r];
-    if (r < R.neq || jar < 0) c += (real)0.5 * R.D[r] * jar * jar;
-  }
+  PmJar<real> j;
+  pm_jar(R, ax, ay, j);
+  c += (real)0.5 * R.wD[0] * j.w[0] * j.w[0];
+  c += (real)0.5 * R.wD[1] * j.w[1] * j.w[1];
+#pragma unroll
+  for (int s = 0; s < PM_MAXACT; s++)
+#pragma unroll
+    for (int e = 0; e < 4; e++)
+      if (s < R.nact && j.p[s][e] < 0) c += (real)0.5 * R.pD[s] * j.p[s][e] * j.p[s][e];
   return c;
 }
 
@@ -104,18 +137,24 @@ __device__ __forceinline__ void pm_solve(const PmParams<real>& P, const PmRows<r
   real cw = pm_cost(P, R, ax, ay), cs = pm_cost(P, R, (real)0, (real)0);
   if (!(cw < cs)) { ax = 0; ay = 0; cw = cs; }
   real cost = cw;
-  real jar[PM_MAXROW], jd[PM_MAXROW];
-  for (int r = 0; r < R.n; r++) jar[r] = R.J[r][0] * ax + R.J[r][1] * ay - R.aref[r];
+  PmJar<real> jar, jd;
+  pm_jar(R, ax, ay, jar);
+  const int nact = R.nact;
   for (int it = 0; it < P.max_iter; it++) {
     real gx = P.m00 * ax + P.m01 * ay, gy = P.m01 * ax + P.m11 * ay;
     real h00 = P.m00, h01 = P.m01, h11 = P.m11;
-    for (int r = 0; r < R.n; r++) {
-      if (r < R.neq || jar[r] < 0) {
-        real dj0 = R.D[r] * R.J[r][0], dj1 = R.D[r] * R.J[r][1];
-        gx += dj0 * jar[r]; gy += dj1 * jar[r];
-        h00 += dj0 * R.J[r][0]; h01 += dj0 * R.J[r][1]; h11 += dj1 * R.J[r][1];
-      }
-    }
+    // weld rows: J = -e_i, always active
+    gx += -R.wD[0] * jar.w[0]; h00 += R.wD[0];
+    gy += -R.wD[1] * jar.w[1]; h11 += R.wD[1];
+#pragma unroll
+    for (int s = 0; s < PM_MAXACT; s++)
+#pragma unroll
+      for (int e = 0; e < 4; e++)
+        if (s < nact && jar.p[s][e] < 0) {
+          real dj0 = R.pD[s] * R.pJ[s][e][0], dj1 = R.pD[s] * R.pJ[s][e][1];
+          gx += dj0 * jar.p[s][e]; gy += dj1 * jar.p[s][e];
+          h00 += dj0 * R.pJ[s][e][0]; h01 += dj0 * R.pJ[s][e][1]; h11 += dj1 * R.pJ[s][e][1];
+        }
     if (sqrt(gx * gx + gy * gy) * P.scale < P.tol) break;
     real det = h00 * h11 - h01 * h01;
     real dx = -(h11 * gx - h01 * gy) / det, dy = -(-h01 * gx + h00 * gy) / det;
@@ -123,37 +162,51 @@ __device__ __forceinline__ void pm_solve(const PmParams<real>& P, const PmRows<r
     real Mdx = P.m00 * dx + P.m01 * dy, Mdy = P.m01 * dx + P.m11 * dy;
     real sl = dx * (P.m00 * ax + P.m01 * ay) + dy * (P.m01 * ax + P.m11 * ay);
     real cu = dx * Mdx + dy * Mdy;
-    for (int r = 0; r < R.n; r++) {
-      real t = R.J[r][0] * dx + R.J[r][1] * dy;
-      jd[r] = t;
-      bool act = r < R.neq || jar[r] < 0 || (jar[r] == 0 && t < 0);
-      if (act) { sl += R.D[r] * jar[r] * t; cu += R.D[r] * t * t; }
-    }
+    jd.w[0] = -dx; jd.w[1] = -dy;
+    sl += R.wD[0] * jar.w[0] * jd.w[0]; cu += R.wD[0] * jd.w[0] * jd.w[0];
+    sl += R.wD[1] * jar.w[1] * jd.w[1]; cu += R.wD[1] * jd.w[1] * jd.w[1];
+#pragma unroll
+    for (int s = 0; s < PM_MAXACT; s++)
+#pragma unroll
+      for (int e = 0; e < 4; e++) {
+        real t = R.pJ[s][e][0] * dx + R.pJ[s][e][1] * dy;
+        jd.p[s][e] = t;
+        bool act = s < nact && (jar.p[s][e] < 0 || (jar.p[s][e] == 0 && t < 0));
+        if (act) { sl += R.pD[s] * jar.p[s][e] * t; cu += R.pD[s] * t * t; }
+      }
     // walk the breakpoints alpha_r = -jar/jd in ascending order
     real alpha = 0, best = -1;
-    for (int guard = 0; guard <= R.n; guard++) {
+    for (int guard = 0; guard <= 4 * nact; guard++) {
       if (sl >= 0) { best = alpha; break; }
       real next = (real)1e30;
-      int rn = -1;
-      for (int r = R.neq; r < R.n; r++) {
-        if (jd[r] == 0) continue;
-        real al = -jar[r] / jd[r];
-        if (al > alpha && al < next) { next = al; rn = r; }
-      }
+      bool any = false;
+#pragma unroll
+      for (int s = 0; s < PM_MAXACT; s++)
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          if (s < nact && jd.p[s][e] != 0) {
+            real al = -jar.p[s][e] / jd.p[s][e];
+            if (al > alpha && al < next) { next = al; any = true; }
+          }
+        }
       real astar = alpha - sl / cu;
-      if (astar <= next || rn < 0) { best = astar; break; }
+      if (astar <= next || !any) { best = astar; break; }
       sl += cu * (next - alpha);
       alpha = next;
       // all rows sharing this breakpoint switch together
-      for (int r = R.neq; r < R.n; r++) {
-        if (jd[r] == 0) continue;
-        real al = -jar[r] / jd[r];
-        if (al == next) { real q = R.D[r] * jd[r] * jd[r]; cu += (jd[r] > 0) ? -q : q; }
-      }
+#pragma unroll
+      for (int s = 0; s < PM_MAXACT; s++)
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          if (s < nact && jd.p[s][e] != 0) {
+            real al = -jar.p[s][e] / jd.p[s][e];
+            if (al == next) { real q = R.pD[s] * jd.p[s][e] * jd.p[s][e]; cu += (jd.p[s][e] > 0) ? -q : q; }
+          }
+        }
     }
     if (best < 0) best = alpha;
     ax += best * dx; ay += best * dy;
-    for (int r = 0; r < R.n; r++) jar[r] = R.J[r][0] * ax + R.J[r][1] * ay - R.aref[r];
+    pm_jar(R, ax, ay, jar);
     real nc = pm_cost(P, R, ax, ay);
     real improvement = cost - nc;
     cost = nc;
@@ -269,6 +322,7 @@ __global__ void __launch_bounds__(128) pm_step_kernel(PmParams<real> P, PmIO io)
     // rows left behind by the previous mj_step1: built with the OLD mocap
     PmRows<real> R;
     pm_build_rows<real>(P, (real)qx, (real)qy, (real)vx, (real)vy, (real)mx, (real)my, R);
+    int overflow = R.overflow;
     // before_step: mocap = clip(xpos + action) (point_reach.py:150-163; both axes use X_RANGE)
     mx = fmin(fmax((double)P.body_x + qx + (double)a0, (double)P.lo), (double)P.hi);
     my = fmin(fmax((double)P.body_y + qy + (double)a1, (double)P.lo), (double)P.hi);
@@ -278,6 +332,7 @@ __global__ void __launch_bounds__(128) pm_step_kernel(PmParams<real> P, PmIO io)
       qx += (double)P.timestep * vx; qy += (double)P.timestep * vy;
       time += (double)P.timestep;
       pm_build_rows<real>(P, (real)qx, (real)qy, (real)vx, (real)vy, (real)mx, (real)my, R);  // mj_step1
+      overflow |= R.overflow;
     }
     // after_step + reward/termination (point_reach.py:165-202)
     double px = (double)P.body_x + qx, py = (double)P.body_y + qy;
@@ -304,7 +359,7 @@ __global__ void __launch_bounds__(128) pm_step_kernel(PmParams<real> P, PmIO io)
     if (io.final_obs64) { double* d = io.final_obs64 + 4 * (size_t)e; d[0] = px; d[1] = py; d[2] = tx; d[3] = ty; }
     double o64[4] = {px, py, tx, ty};
     int episode = io.si[PM_I_EPISODE * N + e];
-    int status = io.si[PM_I_STATUS * N + e] | (bad ? MJS_STATUS_NAN : 0);
+    int status = io.si[PM_I_STATUS * N + e] | (bad ? MJS_STATUS_NAN : 0) | (overflow ? MJS_STATUS_CONTACT_OVERFLOW : 0);
     if (last) {
       ret_sum = ret; len_sum = steps; n_ep = 1; n_succ = goal; n_trunc = !goal; n_err = bad;
     }
