@@ -28,10 +28,12 @@ WORKLOADS = {
     "planar_push": ("robot_planar_push", 42624, 0.86e6, 771.0),  # 148 SMs x 12 FP64 warps x 24 waves (launch tail amortised)
     "point_mass_reach": ("point_mass_reach", 65536, 3.6e3, 151.0),
     "robot_reach": ("robot_reach", 16384, 0.115e6, 283.0),
-    "push_button": ("robot_push_button", 4736, 0.58e6, 539.0),
+    "push_button": ("robot_push_button", 4096, 0.58e6, 539.0),  # BASELINE.json configs[4]: 4096 envs per GPU
 }
 METRIC = "env-steps/s (device-timed) Planar Push"
-TRAFFIC_PER_ENV = {"f64": 3158.0, "mixed": 3158.0}  # ncu at 42624 envs: (38.3 MB read + 96.3 MB written) / launch; measured at f64, the mixed kernel moves the same FP64 records
+SMALL_ENVS = 4096   # BASELINE.json configs[3] names "4096 envs per GPU": reported beside the headline as config_4096
+STATS_EVERY = 10    # control steps between two NCCL all-reduces of the statistics vector inside the timed region
+KERNEL_SOURCES = ["arm_kernel.cuh", "arm_model.cuh", "arm_launch.cuh", "arm_sim.cuh", "mjs_common.cuh", "arm.cu"]
 MIXED_ENVS = 37888  # 148 SMs x 16 FP32 warps x 16 waves
 FP32_PEAK_TFLOPS_FALLBACK = 148 * 128 * 2 * 1.965e9 / 1e12  # SMs x FP32 lanes x FMA x clocks.max.sm = 74.4
 
@@ -42,6 +44,46 @@ def _peaks():
         d = json.loads(p.read_text())
         return float(d.get("hbm_gbs", 6650.0)), "measured", float(d.get("sm_max_mhz", 1965.0))
     return 6650.0, "fallback", 1965.0
+
+
+def _fma_peak(precision: str, sm_max: float):
+    """Non-tensor FMA peak in TFLOP/s: measured on this pool's B200 by tools/fma_peak.cu (register-resident FMA chains on
+    all SMs, one launch >= 1 s; profiles/r2/fma_peak.json), else the nominal SMs x lanes x 2 x clock figure."""
+    lanes = 64 if precision == "f64" else 128
+    p = ROOT / "profiles" / "r2" / "fma_peak.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        key = "fp64_fma_tflops" if precision == "f64" else "fp32_fma_tflops"
+        return float(d[key]), f"measured: tools/fma_peak.cu on {d.get('gpu', 'B200')} ({d.get('sms', 148)} SMs), profiles/r2/fma_peak.json"
+    return 148 * lanes * 2 * sm_max * 1e6 / 1e12, f"nominal: 148 SMs x {lanes} lanes x 2 x {sm_max:.0f} MHz (profiles/r2/fma_peak.json missing)"
+
+
+def kernel_source_hash():
+    import hashlib
+
+    h = hashlib.sha256()
+    for f in KERNEL_SOURCES:
+        h.update((ROOT / "mujoco_sim_b200" / "csrc" / f).read_bytes())
+    return h.hexdigest()[:16]
+
+
+def _traffic(precision: str, N: int):
+    """DRAM bytes per launch of the step kernel from the committed ncu --set full capture of this bench command
+    (profiles/r2/traffic.json, written by tools/ncu_traffic.py from the raw ncu page).  The capture names the hash of the
+    kernel sources it was taken from: a capture of other sources is STALE and is not reported."""
+    p = ROOT / "profiles" / "r2" / "traffic.json"
+    if not p.exists():
+        return None, "no ncu capture committed for this round (profiles/r2/traffic.json missing)"
+    d = json.loads(p.read_text()).get(precision)
+    if not d:
+        return None, f"profiles/r2/traffic.json has no {precision} capture"
+    cur = kernel_source_hash()
+    if d.get("kernel_source_hash") != cur:
+        print(f"bench.py: ncu traffic capture is STALE (sources {d.get('kernel_source_hash')}, now {cur}); re-run tools/ncu_bench.sh", file=sys.stderr)
+        return None, f"STALE: capture {d.get('file')} is of kernel sources {d.get('kernel_source_hash')}, the library now builds from {cur}"
+    per_env = float(d["dram_bytes_per_launch"]) / float(d["envs"])
+    return per_env * N, (f"dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full launch of this bench command: {d['dram_bytes_per_launch'] / 1e6:.1f} MB at "
+                         f"{d['envs']} envs = {per_env:.0f} B/env ({d.get('file')}, kernel sources {cur}), scaled to {N} envs; algorithmic 771 B/env")
 
 
 # ----------------------------------------------------------------------------- clocks
@@ -210,14 +252,31 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def timed_region(step_fn, steps):
+    side = torch.cuda.Stream(dev)
+    stat_buf = torch.zeros(8, dtype=torch.float64, device=dev)
+    n_allreduce = [0]
+
+    def stats_allreduce(e):
+        """The path's only collective: snapshot the 8-double statistics vector on a side stream and all-reduce
+        it over NCCL while the step kernels keep running; joined before the region closes."""
+        side.wait_stream(stream)
+        with torch.cuda.stream(side):
+            stat_buf.copy_(e.stats_tensor())
+            if world > 1:
+                dist.all_reduce(stat_buf)
+        n_allreduce[0] += 1
+
+    def timed_region(step_fn, steps, e=None):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for i in range(steps):
             flush.zero_()          # L2 flush between timed iterations (inside the region: ~2% pessimistic)
             step_fn(i)
+            if e is not None and (i + 1) % STATS_EVERY == 0:
+                stats_allreduce(e)
         env.join_aux()             # background reset preparation launched by these steps is part of the job
+        stream.wait_stream(side)   # ... and so are the statistics all-reduces
         e1.record(stream)
         barrier()
         ms_ = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
@@ -235,8 +294,9 @@ def run_gpu(args):
         env.step_flat(actions[i % ring])
     l0 = env.launch_count
     with ClockSampler(local) as clk:
-        t_ms = timed_region(lambda i: env.step_flat(actions[(args.warmup + i) % ring]), args.steps)
+        t_ms = timed_region(lambda i: env.step_flat(actions[(args.warmup + i) % ring]), args.steps, env)
     launches = env.launch_count - l0
+    n_stats = n_allreduce[0]
     # flush cost alone, for the record
     barrier(); f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record(stream)
@@ -297,6 +357,24 @@ def run_gpu(args):
         alt = {"precision": "mixed", "envs_per_gpu": N2, "value": world * N2 * args.steps / (t2 * 1e-3), "unit": "env-steps/s", "ms_per_step": t2 / args.steps,
                "note": "FP32 dynamics/solver + FP64 state; misses the 1e-4 single-step gate on impact steps, reported only"}
 
+    # ---- the same kernel at BASELINE.json's own batch size (4096 envs per GPU): a 2.3-wave launch, tail-dominated
+    small = None
+    if host_actions and not args.envs and not args.no_small:
+        env3 = ms.make(task, SMALL_ENVS, device=dev, seed=args.seed, env_offset=sharding.env_offset(rank, SMALL_ENVS), precision=args.precision)
+        env3.reset()
+        _stagger_episodes(env3, env3.bundle.task.max_steps, args.seed + rank)
+        act3 = actions[:, :SMALL_ENVS].contiguous()
+        for i in range(burn_in + args.warmup):
+            env3.step_flat(act3[i % ring])
+        main_env, env = env, env3
+        t3 = timed_region(lambda i: env3.step_flat(act3[(args.warmup + i) % ring]), args.steps)
+        env = main_env
+        env3.close()
+        v3 = world * SMALL_ENVS * args.steps / (t3 * 1e-3)
+        small = {"envs_per_gpu": SMALL_ENVS, "value": v3, "unit": "env-steps/s", "ms_per_step": t3 / args.steps, "precision": args.precision,
+                 "per_env_rate_vs_headline_batch": v3 / (world * N * args.steps / (t_ms * 1e-3)),
+                 "note": "BASELINE.json configs[3] size; same kernel, same timing method (L2 flush inside the region)"}
+
     # ---- episode statistics: the only collective of the path
     stats = sharding.allreduce_stats(env.stats_tensor())
 
@@ -305,9 +383,9 @@ def run_gpu(args):
     if rank == 0:
         hbm_peak, peak_src, sm_max = _peaks()
         kern_rate = N / (kernel_ms * 1e-3)
-        lanes = 64 if args.precision == "f64" else 128  # FP64 issues at half the FP32 rate on B200
-        fp32_peak = 148 * lanes * 2 * sm_max * 1e6 / 1e12
+        fp32_peak, fma_src = _fma_peak(args.precision, sm_max)
         bound = "fp64" if args.precision == "f64" else "fp32"
+        traffic, traffic_note = _traffic(args.precision, N) if args.workload == "planar_push" else (None, "not captured for this workload")
         out = {
             "metric": METRIC if args.workload == "planar_push" else f"env-steps/s (device-timed) {args.workload}",
             "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -324,13 +402,15 @@ def run_gpu(args):
             "clocks": clk.summary(),
             "roofline": {"bound": bound, "achieved": kern_rate * flops_per / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": kern_rate * flops_per / 1e12 / fp32_peak,
-                         "traffic": (TRAFFIC_PER_ENV[args.precision] * N if args.workload == "planar_push" else None),
-                         "traffic_note": "DRAM bytes per launch = 3.2 kB/env (dram__bytes_read+write of one ncu --set full capture of the bench command at 42624 envs, profiles/r1/prof_f64_v7_raw.csv: state records in and out, reset slots, outputs, write-back of the remaining per-thread stack traffic) x envs; algorithmic 771 B/env",
+                         "traffic": traffic, "traffic_note": traffic_note,
                          "kernel": "arm_step_kernel", "kernel_ms": kernel_ms, "kernel_ms_median": per[len(per) // 2], "flops_per_env_step": flops_per,
-                         "peak_source": f"148 SMs x {lanes} {bound.upper()} lanes x 2 x clocks.max.sm {sm_max:.0f} MHz, nominal non-tensor FMA peak (MEASURED_PEAKS.json has only HBM and bf16 tensor peaks)",
+                         "peak_source": fma_src,
                          "hbm": {"achieved": kern_rate * bytes_per / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": kern_rate * bytes_per / 1e9 / hbm_peak,
                                  "peak_source": peak_src, "bytes_per_env_step": bytes_per}},
             "alt_precision": alt,
+            "config_4096": small,
+            "stats_allreduce": {"every_steps": STATS_EVERY, "count_in_timed_region": n_stats, "bytes": 64,
+                                "how": "NCCL all_reduce(SUM) of the 8-double statistics vector on a side stream, overlapping the step kernels; joined before the closing event"},
             "episode_stats": {k: stats[k] for k in sharding.STAT_KEYS},
         }
     env.close()
@@ -357,7 +437,7 @@ def run_reference(args):
         "warmup": args.warmup, "ms_per_step": 1e3 * n / rate, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic (oracle-settled initial states, uniform random actions in the reachable workspace box)",
         "config": {"workload": f"{args.workload}: UR5e + cylinder pusher + 3 cylinder props, 20 substeps/step; bounded sample of {n} envs per step",
-                   "note": "MuJoCo/dm_control unavailable on this box: CPU restatement (oracle port), Newton solver at MuJoCo's default tolerance 1e-8"},
+                   "note": "MuJoCo/dm_control unavailable on this box: CPU restatement (oracle port, g++ -O3, dense single-env code), Newton solver at MuJoCo's default tolerance 1e-8; NOT the reference's own engine"},
         "cpu_baseline": {"value": rate, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": rate, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -377,6 +457,7 @@ def main():
     ap.add_argument("--burn-in", type=int, default=-1, help="untimed steps before warm-up (default: one episode length + 50 for Planar Push, else 0)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-alt", action="store_true", help="skip the secondary precision=mixed measurement")
+    ap.add_argument("--no-small", action="store_true", help="skip the 4096-envs-per-GPU record (config_4096)")
     ap.add_argument("--cpu-envs-per-core", type=int, default=64)
     ap.add_argument("--cpu-steps", type=int, default=300)
     args = ap.parse_args()

@@ -201,6 +201,8 @@ typedef struct MjsTask {
   double touch_lo;
   double touch_hi;
   int settle_steps;        /* Planar Push: 150 physics steps after placing objects */
+  int button_disturbances; /* Button Push: after_step may deactivate the switch (robot_push_button.py:159-165) */
+  double disturb_prob;     /* ... with this probability per control step (0.01 in the reference) */
 } MjsTask;
 
 /* Logical per-env state (AoS, double).  The oracle steps this struct directly;

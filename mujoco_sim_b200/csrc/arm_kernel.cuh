@@ -1812,7 +1812,7 @@ struct ArmTask {
   }
 
   // One control step for the env owned by this warp (composer loop)
-  __device__ static void control_step(const AM& A, WM& W, int lane, TS& T, real& a_i, const double* action, Out& o) {
+  __device__ static void control_step(const AM& A, WM& W, int lane, TS& T, real& a_i, const double* action, Out& o, const ArmIO& io, int e) {
     if (A.kind == MJS_TASK_REACH) servoL(A, W, lane, T, action);
     else if (A.kind == MJS_TASK_PUSH) {
       T.step += 1;
@@ -1833,6 +1833,11 @@ struct ArmTask {
       o.h4 += so.niter >= 3; o.h8 += so.niter >= 6; o.h16 += so.niter >= 12; o.h32 += so.niter >= 30;
 #endif
       if (A.kind == MJS_TASK_BUTTON) switch_update(A, T, so.touch);
+    }
+    // after_step (robot_push_button.py:159-165): an active, unpressed switch is deactivated with probability disturb_prob;
+    // the draw is keyed by (seed, global env, episode, control step of the episode) on the DISTURB stream
+    if (A.kind == MJS_TASK_BUTTON && A.button_disturbances && T.swa && !T.swp) {
+      if (uniform(io, io.env_offset + e, (unsigned)T.episode, MJS_RNG_DISTURB, (unsigned)T.len, 0.0, 1.0) < A.disturb_prob) T.swa = 0;
     }
     E::kinematics_only(&W, lane);
     observe(A, W, T, o);
@@ -2056,7 +2061,7 @@ __device__ __noinline__ void arm_settle_job(const ArmModel<real>& A, WarpMem<rea
 // One control step of env e by the calling warp (valid == false: a surplus warp of a lock-step block
 // shadowing the last env so that barrier counts match; it writes nothing).
 template <typename real, int NOBJ, bool SYNC>
-__device__ __noinline__ void arm_step_env(const ArmModel<real>& A, WarpMem<real, NOBJ>& W, const ArmIO& io, int e, bool valid, int lane) {
+__device__ __noinline__ void arm_step_env(const ArmModel<real>& A, WarpMem<real, NOBJ>& W, const ArmIO& io, int e, bool valid, int lane, double* bstat) {
   using TK = ArmTask<real, NOBJ>;
   typename TK::TS T;
   real a_i;
@@ -2081,7 +2086,7 @@ __device__ __noinline__ void arm_step_env(const ArmModel<real>& A, WarpMem<real,
     }
   }
   typename TK::Out o;
-  TK::control_step(A, W, lane, T, a_i, action, o);
+  TK::control_step(A, W, lane, T, a_i, action, o, io, e);
   if (!valid) return;  // all barriers of this launch are behind us
   if (io.times && lane == 0) {
     long long t1; unsigned smid;
@@ -2107,16 +2112,18 @@ __device__ __noinline__ void arm_step_env(const ArmModel<real>& A, WarpMem<real,
     if (io.reward) io.reward[e] = (float)o.reward;
     if (io.reward64) io.reward64[e] = o.reward;
     if (io.flags) reinterpret_cast<uchar4*>(io.flags)[e] = make_uchar4(o.terminated, o.truncated, o.success, o.done);
+    // statistics go to the block's shared accumulator (one global atomic per counter and block at the end of the kernel,
+    // SURVEY.md 8e) instead of two same-address global atomics per env and launch
     if (io.stats) {  // solver effort: env-substeps and Newton iterations (mjs_stats slots 6 and 7)
-      atomicAdd(io.stats + 6, (double)A.n_sub); atomicAdd(io.stats + 7, (double)o.nit_sum);
+      atomicAdd(bstat + 6, (double)A.n_sub); atomicAdd(bstat + 7, (double)o.nit_sum);
 #ifdef MJS_NIT_HIST
-      atomicAdd(io.stats + 2, (double)o.h4); atomicAdd(io.stats + 3, (double)o.h8); atomicAdd(io.stats + 4, (double)o.h16); atomicAdd(io.stats + 5, (double)o.h32);
+      atomicAdd(bstat + 2, (double)o.h4); atomicAdd(bstat + 3, (double)o.h8); atomicAdd(bstat + 4, (double)o.h16); atomicAdd(bstat + 5, (double)o.h32);
 #endif
     }
     if (o.done && io.stats) {
-      atomicAdd(io.stats + 0, T.ret); atomicAdd(io.stats + 1, (double)T.len); atomicAdd(io.stats + 2, 1.0);
-      atomicAdd(io.stats + 3, (double)o.success); atomicAdd(io.stats + 4, (double)o.truncated);
-      atomicAdd(io.stats + 5, (T.status | W.status) ? 1.0 : 0.0);
+      atomicAdd(bstat + 0, T.ret); atomicAdd(bstat + 1, (double)T.len); atomicAdd(bstat + 2, 1.0);
+      atomicAdd(bstat + 3, (double)o.success); atomicAdd(bstat + 4, (double)o.truncated);
+      atomicAdd(bstat + 5, (T.status | W.status) ? 1.0 : 0.0);
     }
   }
   if (o.done && io.autoreset) {
@@ -2180,29 +2187,31 @@ __global__ void __launch_bounds__(WPB * 32) arm_step_kernel(ArmIO io) {
   WM* wm = reinterpret_cast<WM*>(smem_raw);
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   WM& W = wm[warp];
+  // block-level statistics accumulator: every warp reaches both block barriers (no early exit from this kernel)
+  __shared__ double bstat[8];
+  if (threadIdx.x < 8) bstat[threadIdx.x] = 0;
+  __syncthreads();
   if (io.queue) {
     const int njob = io.job_blocks * WPB, total = njob + io.N;
     for (;;) {
       int item = 0;
       if (lane == 0) item = atomicAdd(io.queue, 1);
       item = __shfl_sync(FULLMASK, item, 0);
-      if (item >= total) return;
+      if (item >= total) break;
       if (item < njob) arm_settle_job<real, NOBJ>(A, W, io, item, lane);
-      else arm_step_env<real, NOBJ, SYNC>(A, W, io, item - njob, true, lane);  // the host passes sync_level 0 with a queue
+      else arm_step_env<real, NOBJ, SYNC>(A, W, io, item - njob, true, lane, bstat);  // the host passes sync_level 0 with a queue
       __syncwarp();
     }
-  }
-  if ((int)blockIdx.x < io.job_blocks) {  // the first blocks of the grid prepare next-episode slots (no lock-step)
+  } else if ((int)blockIdx.x < io.job_blocks) {  // the first blocks of the grid prepare next-episode slots (no lock-step)
     arm_settle_job<real, NOBJ>(A, W, io, blockIdx.x * WPB + warp, lane);
-    return;
+  } else {
+    int e = ((int)blockIdx.x - io.job_blocks) * WPB + warp;
+    bool valid = e < io.N;
+    // lock-step mode: surplus warps shadow the last env (barrier counts must match), write nothing
+    if (valid || SYNC) arm_step_env<real, NOBJ, SYNC>(A, W, io, valid ? e : io.N - 1, valid, lane, bstat);
   }
-  int e = ((int)blockIdx.x - io.job_blocks) * WPB + warp;
-  bool valid = e < io.N;
-  if (!valid) {
-    if (!SYNC) return;
-    e = io.N - 1;  // lock-step mode: surplus warps shadow the last env (barrier counts must match), write nothing
-  }
-  arm_step_env<real, NOBJ, SYNC>(A, W, io, e, valid, lane);
+  __syncthreads();
+  if (io.stats && threadIdx.x < 8 && bstat[threadIdx.x] != 0) atomicAdd(io.stats + threadIdx.x, bstat[threadIdx.x]);
 }
 
 // refill == 0: reset the masked envs in place (mjs_reset).

@@ -64,7 +64,8 @@ struct ArmModel {
   double control_dt, time_limit, goal_threshold, target_radius, nearest_coef, tcp_z;
   double spawn_lo[3], spawn_hi[3], target_lo[3], target_hi[3], obj_lo[3], obj_hi[3], action_lo[8], action_hi[8];
   double obj_radius, ik_dh[6], button_goal[3], button_goal_radius, touch_lo, touch_hi;
-  int settle_steps, pad;
+  int settle_steps, button_disturbances;
+  double disturb_prob;
 };
 
 // ------------------------------------------------------------------ host build
@@ -322,6 +323,7 @@ int build_arm_model(const MjsModel& m, const MjsTask& t, int precision_f64, ArmM
   for (int k = 0; k < 8; k++) { A.action_lo[k] = t.action_lo[k]; A.action_hi[k] = t.action_hi[k]; }
   for (int k = 0; k < 6; k++) A.ik_dh[k] = t.ik_dh[k];
   A.button_goal_radius = t.button_goal_radius; A.touch_lo = t.touch_lo; A.touch_hi = t.touch_hi; A.settle_steps = t.settle_steps;
+  A.button_disturbances = t.button_disturbances; A.disturb_prob = t.disturb_prob;
 #undef FAIL
   return 0;
 }

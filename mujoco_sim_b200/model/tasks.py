@@ -308,9 +308,10 @@ def build_robot_reach(config: RobotReachConfig | None = None) -> TaskBundle:
     return TaskBundle("robot_reach", comp, t, keys, np.array(lo, np.float64), np.array(hi, np.float64), np.float64)
 
 
-def build_push_button(max_steps: int = 100) -> TaskBundle:
+def build_push_button(max_steps: int = 100, button_disturbances: bool = False) -> TaskBundle:
     """RobotPushButtonTask scene (robot_push_button.py:56-119, props/switch.py:17-41),
-    state observations, ABS_JOINT_ACTION; rigid gripper."""
+    state observations, ABS_JOINT_ACTION; rigid gripper.  button_disturbances
+    (robot_push_button.py:56,159-165): an active, unpressed switch deactivates with probability 0.01 per control step."""
     world = S.Body("world")
     _arena_plane(world)
     w3, acts = _ur5e(world)
@@ -334,6 +335,8 @@ def build_push_button(max_steps: int = 100) -> TaskBundle:
     t.set("button_goal", (-0.3, -0.2, 0.3))
     t.button_goal_radius = 0.05
     t.touch_lo, t.touch_hi = 5.0, 200.0
+    t.button_disturbances = int(bool(button_disturbances))
+    t.disturb_prob = 0.01
     # synthetic rollouts: q_now +- 0.05 rad handled on device; box kept for the gripper dof
     t.set("action_lo", [-0.05] * 6 + [0.0]); t.set("action_hi", [0.05] * 6 + [0.085])
     keys = [("ur5e/joint_configuration", 6), ("unnamed_model/position", 3), ("unnamed_model/active", 1)]

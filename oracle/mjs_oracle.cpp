@@ -1405,6 +1405,9 @@ void write_obs_reward(const MjsModel* m, const MjsTask* t, MjsEnvState* s, const
 // touch-sensor force after every substep of the last control_step on this thread (test hook: margin of the 5 N / 200 N
 // thresholds of switch.py:51-60, so flag comparisons can exclude envs that sit on a threshold)
 static thread_local double g_touch_trace[64];
+// uniform draw of the button-disturbance test of the current control step (robot_push_button.py:159-165 `random_state.rand()`),
+// supplied by the caller (oracle_control_step_disturb); 1.0 = never
+static thread_local double g_disturb_u = 1.0;
 
 void control_step(const MjsModel* m, const MjsTask* t, MjsEnvState* s, const double* action, MjsStepOut* out, double tol_scale, long* flops) {
   static thread_local Data d;
@@ -1435,6 +1438,7 @@ void control_step(const MjsModel* m, const MjsTask* t, MjsEnvState* s, const dou
     if (t->kind == MJS_TASK_BUTTON) switch_update(t, s, d.touch);
   }
   // ---- after_step
+  if (t->kind == MJS_TASK_BUTTON && t->button_disturbances && s->sw_active && !s->sw_pressed && g_disturb_u < t->disturb_prob) s->sw_active = 0;
   if (t->kind == MJS_TASK_POINTMASS) {
     const double* xp = d.xpos + 3 * t->pm_body;  // point_reach.py:165-170
     s->prev_dist = s->dist;
@@ -1460,6 +1464,15 @@ extern "C" {
 // one control step for n envs (AoS states), OpenMP-free; callers thread by range
 void oracle_control_step(const MjsModel* m, const MjsTask* t, MjsEnvState* states, const double* actions, MjsStepOut* outs, int n, double tol_scale, long* flops) {
   for (int e = 0; e < n; e++) control_step(m, t, states + e, actions + (size_t)e * t->action_dim, outs + e, tol_scale, flops);
+}
+
+// oracle_control_step with the button-disturbance draw of every env supplied by the caller: u[n] in [0, 1)
+void oracle_control_step_disturb(const MjsModel* m, const MjsTask* t, MjsEnvState* states, const double* actions, MjsStepOut* outs, int n, double tol_scale, const double* u) {
+  for (int e = 0; e < n; e++) {
+    g_disturb_u = u[e];
+    control_step(m, t, states + e, actions + (size_t)e * t->action_dim, outs + e, tol_scale, nullptr);
+  }
+  g_disturb_u = 1.0;
 }
 
 // oracle_control_step that also returns the touch-sensor force after every substep: touch[n][n_sub]

@@ -66,6 +66,16 @@ class OracleEnvs:
         )
         return self.collect()
 
+    def step_disturb(self, actions, u):
+        """step() with the button-disturbance draw u[n] of this control step (robot_push_button.py:159-165)"""
+        a = np.ascontiguousarray(actions, dtype=np.float64).reshape(self.n, self.task.action_dim)
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        lib().oracle_control_step_disturb(
+            ctypes.byref(self.model), ctypes.byref(self.task), self.states, _dp(a), self.outs, self.n,
+            ctypes.c_double(self.tol_scale), _dp(u),
+        )
+        return self.collect()
+
     def step_touch(self, actions):
         """step() that also returns the touch-sensor force after every substep: (collect(), touch[n, n_sub])"""
         a = np.ascontiguousarray(actions, dtype=np.float64).reshape(self.n, self.task.action_dim)

@@ -8,7 +8,7 @@ import numpy as np
 
 M0, M1, W0, W1 = 0xD2511F53, 0xCD9E8D57, 0x9E3779B9, 0xBB67AE85
 MASK = 0xFFFFFFFF
-RNG_RESET, RNG_ACTION = 1, 2
+RNG_RESET, RNG_ACTION, RNG_DISTURB = 1, 2, 3
 
 
 def philox4x32_10(c0, c1, c2, c3, k0, k1):
@@ -79,3 +79,8 @@ def push_reset_state(bundle, state, seed, genv, episode):
         state.target[k] = target[k]
     state.episode_id = episode
     return spawn, target, pos
+
+
+def button_disturb_u(seed, genv, episode, step_in_episode):
+    """the uniform draw of the button-disturbance test (arm_kernel.cuh control_step, restating robot_push_button.py:159-165)"""
+    return uniform(seed, genv, episode, RNG_DISTURB, step_in_episode, 0.0, 1.0)

@@ -231,3 +231,39 @@ def test_button_f64_scripted_rollout_flags_are_exact_on_1024_envs():
     assert nexcl <= n // 100
     assert worst_q < TOL_CONTACT_STEP
     env.close()
+
+
+def test_button_disturbances_follow_the_reference_rule_and_the_oracle():
+    """robot_push_button.py:159-165: after every control step an active, unpressed switch is deactivated with probability
+    p (0.01 in the reference; 0.2 here so that a short rollout sees many).  The device draws from the Philox DISTURB stream
+    keyed by (seed, env, episode, control step); the oracle is handed the same draws (tests/philox_ref.py)."""
+    import mujoco_sim_b200 as ms
+    from mujoco_sim_b200.model.tasks import build_push_button
+    from tests.philox_ref import button_disturb_u
+
+    n, steps, seed = 256, 60, 77
+    b = build_push_button(button_disturbances=True)
+    b.task.disturb_prob = 0.2
+    ora = arm_states(b, n, 10)
+    ms.envs.register_builder("_button_disturbed", lambda: b)
+    env = ms.BatchedMujocoSimEnv("_button_disturbed", n, precision="f64", autoreset=False, seed=seed)
+    env.set_state(copy_states(ora.states, n), forward=True)
+    ndeact = 0
+    alive = np.ones(n, bool)
+    for k in range(steps):
+        a, _ = ora.demo_policy()
+        a = a.astype(np.float32)
+        was = ora.field("sw_active").copy()
+        u = np.array([button_disturb_u(seed, e, int(ora.states[e].episode_id), k) for e in range(n)])
+        obs_o, rew_o, _, fl_o = ora.step_disturb(a.astype(np.float64), u)
+        env.step(torch.from_numpy(a).cuda())
+        st = env.get_state()
+        swa = np.array([s.sw_active for s in st]); swp = np.array([s.sw_pressed for s in st])
+        np.testing.assert_array_equal(swa[alive], ora.field("sw_active")[alive], err_msg=f"active differs at step {k}")
+        np.testing.assert_array_equal(env._flags.cpu().numpy()[alive], fl_o[alive])
+        np.testing.assert_array_equal(env._obs.cpu().numpy()[alive, 9], obs_o[alive, 9].astype(np.float32))
+        ndeact += int(((was == 1) & (ora.field("sw_active") == 0) & (ora.field("sw_pressed") == 0) & (u < 0.2))[alive].sum())
+        alive &= ~fl_o[:, 3].astype(bool)
+    print("button disturbances: deactivations", ndeact, "over", steps, "steps x", n, "envs")
+    assert ndeact > 20
+    env.close()

@@ -2,7 +2,7 @@
 # ncu evidence for the bench command (run under gpurun).  $1 = precision.  Writes CSV pages (the
 # .ncu-rep is too large to travel back: gpurun_out is capped at 64 MiB).
 P=${1:-f64}
-CMD="python bench.py --steps 4 --warmup 3 --precision $P --no-cpu-baseline --no-alt $BENCH_EXTRA"
+CMD="python bench.py --steps 4 --warmup 3 --precision $P --no-cpu-baseline --no-alt --no-small $BENCH_EXTRA"
 $CMD > gpurun_out/plain_$P.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches_$P.csv $CMD > gpurun_out/ncu_list_$P.log 2>&1
 $CMD > gpurun_out/plain2_$P.log 2>&1 &&
