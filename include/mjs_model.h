@@ -245,4 +245,33 @@ typedef struct MjsStepOut {
   int done;
 } MjsStepOut;
 
+/* ---- camera observations as ray casting (replaces entities/camera.py:76-103 `physics.render`) ---- */
+#define MJS_MAXVIS 32
+#define MJS_ANCHOR_WORLD 0   /* pose given in the world frame */
+#define MJS_ANCHOR_GEOM 1    /* pose of model geom `geom` (its own pos/quat/size; `pos`/`quat` unused) */
+#define MJS_ANCHOR_TARGET 2  /* translated to the env's task target (state.target; z from `pos[2]` when the target is planar) */
+#define MJS_ANCHOR_OVR 3     /* translated by the env's overridable body position (Button Push switch) */
+#define MJS_ANCHOR_GEOMFRAME 4 /* `pos`/`quat` are local to the frame of model geom `geom` (wrist camera) */
+/* One visible primitive: a model geom, or a marker (target site, switch parts) that follows per-env state. */
+typedef struct MjsVisual {
+  int type;              /* MJS_GEOM_* */
+  int geom;              /* model geom index for MJS_ANCHOR_GEOM / GEOMFRAME, else -1 */
+  int anchor;
+  int use_active;        /* 1: colour is rgba_active while the env's switch is active (props/switch.py:59) */
+  double pos[3];
+  double quat[4];
+  double size[3];
+  double rgba[4];
+  double rgba_active[4];
+} MjsVisual;
+
+/* Fixed camera (entities/camera.py:86-88: mode="fixed", looks along its -z axis, +y up), optionally riding on a geom frame. */
+typedef struct MjsCamera {
+  int anchor;            /* MJS_ANCHOR_WORLD or MJS_ANCHOR_GEOMFRAME */
+  int geom;
+  double pos[3];
+  double quat[4];
+  double fovy;           /* vertical field of view, degrees */
+} MjsCamera;
+
 #endif /* MJS_MODEL_H_ */

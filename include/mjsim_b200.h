@@ -111,6 +111,14 @@ int mjs_demo_policy(MjsSim* sim, double noise, float* d_actions, int* d_ok, void
  * {start ns, end of control step ns, end ns, newton_iterations << 32 | max_iterations << 16 | smid} of the last launch. */
 int mjs_debug_times(MjsSim* sim, long long* h_out, int n);
 
+/* Replaces: Camera.get_rgb_image -> physics.render(height, width, camera_id) (entities/camera.py:94-103; the RGB observables
+ * of point_reach.py:22,95-98, robot_reach.py:52,116-118, robot_planar_push.py:42-43, robot_push_button.py:87-96).  Ray-casts
+ * the current state of every env from a fixed camera: d_rgb [N][height][width][3] uint8, channel-last like the reference.
+ * The visible primitives are given by the caller (model geoms by index, markers that follow the env's target / switch);
+ * shading model and limits are stated in csrc/render.cuh.  MuJoCo's OpenGL output is unavailable on this box and is not
+ * reproduced bit for bit.  Allocates its pose scratch on the first call. */
+int mjs_render(MjsSim* sim, const MjsCamera* cam, const MjsVisual* vis, int nvis, int width, int height, unsigned char* d_rgb, void* stream);
+
 /* Number of kernels this library launched since creation (bench `gpu_launches`). */
 long long mjs_launch_count(const MjsSim* sim);
 int mjs_num_envs(const MjsSim* sim);

@@ -8,6 +8,7 @@
 #include "../../include/mjsim_b200.h"
 #include "mjs_common.cuh"
 #include "pointmass.cuh"
+#include "render.cuh"
 #include "arm_api.cuh"
 
 static thread_local char g_err[1024] = "";
@@ -28,6 +29,7 @@ struct MjsSim {
   double* d_stats;
   // host-call staging (pinned host + device)
   float *d_act, *d_obs, *d_rew, *d_fobs;
+  float *d_gpose, *d_aux;  // mjs_render scratch, allocated at the first call
   double *obs64, *rew64, *fobs64;  // caller-owned float64 outputs registered by mjs_set_output64 (may be null)
   unsigned char *d_flags, *d_mask;
   cudaStream_t hstream;
@@ -204,7 +206,7 @@ void mjs_destroy(MjsSim* s) {
   if (!s) return;
   DeviceGuard guard(s->device);
   cudaFree(s->d_stats); cudaFree(s->d_act); cudaFree(s->d_obs); cudaFree(s->d_fobs); cudaFree(s->d_rew); cudaFree(s->d_flags); cudaFree(s->d_mask);
-  cudaFree(s->pm_sd); cudaFree(s->pm_si);
+  cudaFree(s->pm_sd); cudaFree(s->pm_si); cudaFree(s->d_gpose); cudaFree(s->d_aux);
   if (s->arm) arm_destroy(s->arm);
   cudaStreamDestroy(s->hstream);
   delete s;
@@ -379,6 +381,76 @@ int mjs_debug_times(MjsSim* s, long long* h_out, int n) {
   if (!s->arm) { mjs_set_error("mjs_debug_times: articulated tasks only"); return -1; }
   DeviceGuard guard(s->device);
   return arm_debug_times(s->arm, h_out, n);
+}
+
+static void h_mulquat(double* r, const double* a, const double* b) {
+  r[0] = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3]; r[1] = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+  r[2] = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1]; r[3] = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+}
+
+int mjs_render(MjsSim* s, const MjsCamera* cam, const MjsVisual* vis, int nvis, int width, int height, unsigned char* d_rgb, void* stream) {
+  DeviceGuard guard(s->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (nvis < 0 || nvis > MJS_MAXVIS) { mjs_set_error("mjs_render: %d visuals exceed MJS_MAXVIS = %d", nvis, MJS_MAXVIS); return -1; }
+  if (width <= 0 || height <= 0 || width > 4096 || height > 4096) { mjs_set_error("mjs_render: bad image size %d x %d", width, height); return -1; }
+  if (!d_rgb || !cam || (!vis && nvis)) { mjs_set_error("mjs_render: null argument"); return -1; }
+  const int N = s->N, ng = s->model.ngeom;
+  RenderScene S;
+  memset(&S, 0, sizeof(S));
+  S.nvis = nvis; S.width = width; S.height = height;
+  auto norm_quat_mat = [](const double* q, float* m) {
+    double n = std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]), u[4] = {1, 0, 0, 0}, md[9];
+    if (n > 0) for (int k = 0; k < 4; k++) u[k] = q[k] / n;
+    h_quat2mat(md, u);
+    for (int k = 0; k < 9; k++) m[k] = (float)md[k];
+  };
+  for (int i = 0; i < nvis; i++) {
+    const MjsVisual& v = vis[i];
+    RenderVis& r = S.vis[i];
+    r.type = v.type; r.geom = v.geom; r.anchor = v.anchor; r.use_active = v.use_active;
+    if ((v.anchor == MJS_ANCHOR_GEOM || v.anchor == MJS_ANCHOR_GEOMFRAME) && (v.geom < 0 || v.geom >= ng)) { mjs_set_error("mjs_render: visual %d names geom %d of %d", i, v.geom, ng); return -1; }
+    if (v.type != MJS_GEOM_PLANE && v.type != MJS_GEOM_SPHERE && v.type != MJS_GEOM_CAPSULE && v.type != MJS_GEOM_CYLINDER && v.type != MJS_GEOM_BOX) { mjs_set_error("mjs_render: visual %d has unsupported type %d", i, v.type); return -1; }
+    for (int k = 0; k < 3; k++) { r.pos[k] = (float)v.pos[k]; r.size[k] = (float)v.size[k]; r.rgb[k] = (float)v.rgba[k]; r.rgb_active[k] = (float)v.rgba_active[k]; }
+    norm_quat_mat(v.quat, r.mat);
+  }
+  S.cam_anchor = cam->anchor; S.cam_geom = cam->geom;
+  if (cam->anchor == MJS_ANCHOR_GEOMFRAME && (cam->geom < 0 || cam->geom >= ng)) { mjs_set_error("mjs_render: camera names geom %d of %d", cam->geom, ng); return -1; }
+  for (int k = 0; k < 3; k++) S.cam_pos[k] = (float)cam->pos[k];
+  norm_quat_mat(cam->quat, S.cam_mat);
+  S.tan_half_fovy = (float)std::tan(0.5 * cam->fovy * 3.14159265358979323846 / 180.0);
+  if (!s->d_gpose) {
+    MJS_CUDA_CHECK(cudaMalloc(&s->d_gpose, sizeof(float) * 12 * MJS_MAXGEOM * (size_t)N));
+    MJS_CUDA_CHECK(cudaMalloc(&s->d_aux, sizeof(float) * 8 * (size_t)N));
+  }
+  if (s->arm) {
+    int r = arm_poses(s->arm, s->d_gpose, s->d_aux, st);
+    if (r < 0) return r;
+    s->launches += r;
+  } else {
+    // PointMass: world pose of every geom at q = 0 (bodies are children of the world, unrotated: build_pm_params checks)
+    PmPoseTable T;
+    memset(&T, 0, sizeof(T));
+    T.ngeom = ng;
+    for (int g = 0; g < ng; g++) {
+      int b = s->model.geom_body[g];
+      double q[4], m[9];
+      h_mulquat(q, s->model.body_quat + 4 * b, s->model.geom_quat + 4 * g);
+      h_quat2mat(m, q);
+      double bm[9], p[3];
+      h_quat2mat(bm, s->model.body_quat + 4 * b);
+      for (int k = 0; k < 3; k++) p[k] = s->model.body_pos[3 * b + k] + bm[3 * k] * s->model.geom_pos[3 * g] + bm[3 * k + 1] * s->model.geom_pos[3 * g + 1] + bm[3 * k + 2] * s->model.geom_pos[3 * g + 2];
+      for (int k = 0; k < 3; k++) T.base[g][k] = (float)p[k];
+      for (int k = 0; k < 9; k++) T.base[g][3 + k] = (float)m[k];
+      T.moves[g] = b == s->task.pm_body;
+    }
+    pm_pose_kernel<<<(N + 127) / 128, 128, 0, st>>>(T, s->pm_sd, N, s->d_gpose, s->d_aux);
+    s->launches++;
+  }
+  dim3 grid(N, (width * height + 127) / 128);
+  render_kernel<<<grid, 128, 0, st>>>(S, s->d_gpose, s->d_aux, d_rgb);
+  s->launches++;
+  MJS_CUDA_CHECK(cudaGetLastError());
+  return 0;
 }
 
 int mjs_set_output64(MjsSim* s, double* d_obs64, double* d_reward64, double* d_final_obs64) {

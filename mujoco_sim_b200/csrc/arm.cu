@@ -175,6 +175,12 @@ int arm_step_noalloc(ArmSim* a, const float* d_actions, float* d_obs, float* d_r
   return dispatch(a, 0, io, st);
 }
 
+int arm_poses(ArmSim* a, float* d_gpose, float* d_aux, cudaStream_t st) {
+  ArmIO io = make_io(a);
+  io.gpose = d_gpose; io.aux = d_aux;
+  return dispatch(a, 6, io, st);
+}
+
 void arm_set_output64(ArmSim* a, double* d_obs64, double* d_reward64, double* d_final_obs64) {
   a->obs64 = d_obs64; a->reward64 = d_reward64; a->final_obs64 = d_final_obs64;
 }

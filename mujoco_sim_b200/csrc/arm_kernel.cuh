@@ -1654,6 +1654,8 @@ struct ArmIO {
   int* njobs_next;  // the other counter of the ping-pong pair, cleared for the next launch
   int job_cap, job_blocks;
   int* queue;       // non-null: persistent step grid, warps pull work items from this counter (zeroed before the launch)
+  float* gpose;      // mjs_render: world pose of every model geom [N][MJS_MAXGEOM][12] (pos 3, mat 9)
+  float* aux;        // mjs_render: per-env anchors [N][8]: target xyz, switch xyz, switch active
   long long* times;  // test hook (mjs_debug_times): per env {start, end of control step, end, nit_sum<<32 | nit_max<<16 | smid} in ns
 };
 
@@ -2308,6 +2310,35 @@ __global__ void __launch_bounds__(WPB * 32) arm_policy_kernel(ArmIO io, float* a
     actions[(size_t)e * A.action_dim + lane] = (float)v;
   }
   if (ok_out && lane == 0) ok_out[e] = ok ? 1 : 0;
+}
+
+// mjs_render, first half: kinematics of the current state -> world pose of every model geom + the per-env anchors
+template <typename real, int NOBJ, int WPB>
+__global__ void __launch_bounds__(WPB * 32) arm_pose_kernel(ArmIO io) {
+  const ArmModel<real>& A = cmodel<real>();
+  using TK = ArmTask<real, NOBJ>;
+  using E = ArmEngine<real, NOBJ>;
+  using WM = WarpMem<real, NOBJ>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WM* wm = reinterpret_cast<WM*>(smem_raw);
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int e = blockIdx.x * WPB + warp;
+  if (e >= io.N) return;
+  WM& W = wm[warp];
+  typename TK::TS T;
+  real a_i;
+  TK::load(A, W, io, e, lane, T, a_i);
+  E::kinematics_only(&W, lane);
+  float* gp = io.gpose + (size_t)e * MJS_MAXGEOM * 12;
+  if (lane < A.ngeom) {
+    for (int k = 0; k < 3; k++) gp[lane * 12 + k] = (float)W.gpos[lane][k];
+    for (int k = 0; k < 9; k++) gp[lane * 12 + 3 + k] = (float)W.gmat[lane][k];
+  }
+  if (lane == 0) {
+    float* a = io.aux + (size_t)e * 8;
+    for (int k = 0; k < 3; k++) { a[k] = (float)T.target[k]; a[3 + k] = (float)T.ovr[k]; }
+    a[6] = (float)T.swa; a[7] = 0;
+  }
 }
 
 // mj_forward on injected states (mjs_set_state with forward != 0): refresh the warm start

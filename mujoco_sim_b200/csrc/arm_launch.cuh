@@ -77,6 +77,10 @@ static int launch(ArmSim* a, const ArmModel<real>& M, int which, ArmIO io, cudaS
     auto k = arm_policy_kernel<real, NOBJ, ARM_WPB>;
     MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k<<<grid, ARM_WPB * 32, smem, st>>>(io, a->pol_actions, a->pol_ok, a->pol_noise);
+  } else if (which == 6) {
+    auto k = arm_pose_kernel<real, NOBJ, ARM_WPB>;
+    MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid, ARM_WPB * 32, smem, st>>>(io);
   } else if (which == 3) {
     auto k = arm_debug_kernel<real, NOBJ, ARM_WPB>;
     MJS_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

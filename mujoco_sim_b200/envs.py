@@ -173,6 +173,22 @@ class BatchedMujocoSimEnv:
         _lib.check(self._L.mjs_demo_policy(self._h, float(noise), _ptr(self._pol_a), _ptr(self._pol_ok), self._stream()))
         return self._pol_a, self._pol_ok.bool()
 
+    def render(self, camera: Optional[str] = None, width: Optional[int] = None, height: Optional[int] = None, out: Optional[torch.Tensor] = None):
+        """Camera observation of every env (entities/camera.py:94-103 `get_rgb_image`): uint8 [N, H, W, 3], channel-last,
+        ray-cast on the device from the task's fixed camera `camera` (default: the task's first) at the task's resolution."""
+        from .model.cstruct import MjsVisual
+
+        cams = self.bundle.cameras
+        cam = cams[camera] if camera is not None else next(iter(cams.values()))
+        w = int(width or self.bundle.image_resolution); h = int(height or self.bundle.image_resolution)
+        if out is None:
+            out = torch.empty(self.num_envs, h, w, 3, dtype=torch.uint8, device=self.device)
+        assert out.shape == (self.num_envs, h, w, 3) and out.dtype == torch.uint8 and out.is_contiguous()
+        vis = self.bundle.visuals
+        arr = (MjsVisual * max(len(vis), 1))(*vis)
+        _lib.check(self._L.mjs_render(self._h, ctypes.byref(cam), arr, len(vis), w, h, _ptr(out), self._stream()))
+        return out
+
     def join_aux(self):
         """Make the current stream wait for background reset preparation in flight."""
         _lib.check(self._L.mjs_join_aux(self._h, self._stream()))

@@ -45,6 +45,7 @@ _SIGS = {
     "mjs_step_noalloc": (ctypes.c_int, [ctypes.c_void_p] * 6 + [ctypes.c_int, ctypes.c_void_p]),
     "mjs_reseed": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_ulonglong]),
     "mjs_set_output64": (ctypes.c_int, [ctypes.c_void_p] * 4),
+    "mjs_render": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]),
     "mjs_step_host": (ctypes.c_int, [ctypes.c_void_p] * 6 + [ctypes.c_int]),
     "mjs_reset_host": (ctypes.c_int, [ctypes.c_void_p] * 3),
     "mjs_set_state": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(MjsEnvState), ctypes.c_int, ctypes.c_int, ctypes.c_int]),

@@ -100,6 +100,7 @@ class Compiled:
         self.site_id = {}
         self.jnt_qadr = {}
         self.jnt_dadr = {}
+        self.geom_rgba = []  # per compiled geom, for the ray caster (not part of the physics model)
 
 
 def compile_scene(sc: S.Scene) -> Compiled:
@@ -219,6 +220,7 @@ def compile_scene(sc: S.Scene) -> Compiled:
 
     assert nv <= MACROS["MJS_MAXV"] and nq <= MACROS["MJS_MAXQ"], (nv, nq)
     ng = len(geoms)
+    out.geom_rgba = [tuple(float(x) for x in g.rgba) for g in geoms]
     assert ng <= MACROS["MJS_MAXGEOM"], ng
 
     # ------------------------------------------------------------ sizes/options

@@ -83,3 +83,5 @@ MjsModel = _make("MjsModel")
 MjsTask = _make("MjsTask")
 MjsEnvState = _make("MjsEnvState")
 MjsStepOut = _make("MjsStepOut")
+MjsVisual = _make("MjsVisual")
+MjsCamera = _make("MjsCamera")

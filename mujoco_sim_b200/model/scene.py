@@ -46,6 +46,7 @@ class Geom:
     margin: float = 0.0
     gap: float = 0.0
     name: str = ""
+    rgba: Sequence[float] = (0.5, 0.5, 0.5, 1.0)  # MuJoCo's default geom colour; only the ray caster reads it
 
 
 @dataclasses.dataclass

@@ -13,7 +13,7 @@ import numpy as np
 
 from . import scene as S
 from .compiler import Compiled, compile_scene
-from .cstruct import MACROS, MjsTask
+from .cstruct import MACROS, MjsCamera, MjsTask, MjsVisual
 
 # reward types (point_reach.py:11-14, robot_planar_push.py:33-34)
 SPARSE_REWARD = "sparse_reward"
@@ -40,10 +40,74 @@ class TaskBundle:
     action_low: np.ndarray
     action_high: np.ndarray
     action_dtype: type
+    # camera observations: visible primitives and the task's fixed cameras, consumed by mjs_render
+    visuals: list = dataclasses.field(default_factory=list)
+    cameras: dict = dataclasses.field(default_factory=dict)
+    image_resolution: int = 64
 
     @property
     def model(self):
         return self.compiled.model
+
+
+def _camera(pos, quat, fovy, geom=-1):
+    """entities/camera.py:86-88: fixed camera; quaternions in the reference's configs are not unit length (normalised by
+    MuJoCo's compiler, here by mjs_render)."""
+    c = MjsCamera()
+    c.anchor = MACROS["MJS_ANCHOR_GEOMFRAME"] if geom >= 0 else MACROS["MJS_ANCHOR_WORLD"]
+    c.geom = geom
+    c.set("pos", pos); c.set("quat", quat)
+    c.fovy = float(fovy)
+    return c
+
+
+def _qmul(a, b):
+    return np.array([a[0]*b[0]-a[1]*b[1]-a[2]*b[2]-a[3]*b[3], a[0]*b[1]+a[1]*b[0]+a[2]*b[3]-a[3]*b[2],
+                     a[0]*b[2]-a[1]*b[3]+a[2]*b[0]+a[3]*b[1], a[0]*b[3]+a[1]*b[2]-a[2]*b[1]+a[3]*b[0]])
+
+
+def _qrot(q, v):
+    w, x, y, z = q
+    R = np.array([[w*w+x*x-y*y-z*z, 2*(x*y-w*z), 2*(x*z+w*y)], [2*(x*y+w*z), w*w-x*x+y*y-z*z, 2*(y*z-w*x)], [2*(x*z-w*y), 2*(y*z+w*x), w*w-x*x-y*y+z*z]])
+    return R @ np.asarray(v, float)
+
+
+def _in_geom_frame(gp, gq, fp, fq, cp, cq):
+    """pose (cp, cq), given in a frame (fp, fq) of a body, re-expressed in the frame of that body's geom (gp, gq)"""
+    gq, fq, cq = (np.asarray(q, float) / np.linalg.norm(q) for q in (gq, fq, cq))
+    p = np.asarray(fp, float) + _qrot(fq, cp)
+    q = _qmul(fq, cq)
+    gqi = gq * np.array([1, -1, -1, -1])
+    return _qrot(gqi, p - np.asarray(gp, float)), _qmul(gqi, q)
+
+
+def _geom_visuals(comp: Compiled, skip=(), active=None):
+    """one visual per compiled model geom, coloured by its rgba; `active` = {geom name: rgba while the switch is active}"""
+    out = []
+    names = {v: k for k, v in comp.geom_id.items()}
+    m = comp.model
+    for g in range(m.ngeom):
+        if names.get(g) in skip:
+            continue
+        v = MjsVisual()
+        v.type = m.geom_type[g]; v.geom = g; v.anchor = MACROS["MJS_ANCHOR_GEOM"]
+        v.set("quat", (1, 0, 0, 0))
+        v.set("size", [m.geom_size[3 * g + k] for k in range(3)])
+        v.set("rgba", comp.geom_rgba[g]); v.set("rgba_active", comp.geom_rgba[g])
+        if active and names.get(g) in active:
+            v.use_active = 1
+            v.set("rgba_active", active[names[g]])
+        out.append(v)
+    return out
+
+
+def _marker(gtype, size, rgba, anchor, pos=(0, 0, 0)):
+    v = MjsVisual()
+    v.type = gtype; v.geom = -1; v.anchor = MACROS[anchor]
+    v.set("pos", pos); v.set("quat", (1, 0, 0, 0))
+    v.set("size", list(size) + [0.0] * (3 - len(size)))
+    v.set("rgba", rgba); v.set("rgba_active", rgba)
+    return v
 
 
 def _accumulated_step_limit(control_dt: float, physics_dt: float, time_limit: float) -> int:
@@ -79,14 +143,14 @@ def build_pointmass_reach(reward_type: str = DENSE_BIASED_NEG_DISTANCE_REWARD, m
         c = c / s
         return (math.cos(ang / 2), *(math.sin(ang / 2) * c))
 
-    world.geoms.append(S.Geom(S.PLANE, (0.5, 0.5, 0.1), name="ground"))
-    world.geoms.append(S.Geom(S.PLANE, (0.02, 0.5, 0.02), pos=(-0.5, 0, 0.02), quat=zaxis_quat((1, 0, 0)), name="wall_x"))
-    world.geoms.append(S.Geom(S.PLANE, (0.5, 0.02, 0.02), pos=(0, -0.5, 0.02), quat=zaxis_quat((0, 1, 0)), name="wall_y"))
-    world.geoms.append(S.Geom(S.PLANE, (0.02, 0.5, 0.02), pos=(0.5, 0, 0.02), quat=zaxis_quat((-1, 0, 0)), name="wall_neg_x"))
-    world.geoms.append(S.Geom(S.PLANE, (0.5, 0.02, 0.02), pos=(0, 0.5, 0.02), quat=zaxis_quat((0, -1, 0)), name="wall_neg_y"))
+    world.geoms.append(S.Geom(S.PLANE, (0.5, 0.5, 0.1), name="ground", rgba=(0.15, 0.25, 0.35, 1)))  # mean of the checker texture
+    world.geoms.append(S.Geom(S.PLANE, (0.02, 0.5, 0.02), pos=(-0.5, 0, 0.02), quat=zaxis_quat((1, 0, 0)), name="wall_x", rgba=(0.3, 0.5, 0.7, 1)))
+    world.geoms.append(S.Geom(S.PLANE, (0.5, 0.02, 0.02), pos=(0, -0.5, 0.02), quat=zaxis_quat((0, 1, 0)), name="wall_y", rgba=(0.3, 0.5, 0.7, 1)))
+    world.geoms.append(S.Geom(S.PLANE, (0.02, 0.5, 0.02), pos=(0.5, 0, 0.02), quat=zaxis_quat((-1, 0, 0)), name="wall_neg_x", rgba=(0.3, 0.5, 0.7, 1)))
+    world.geoms.append(S.Geom(S.PLANE, (0.5, 0.02, 0.02), pos=(0, 0.5, 0.02), quat=zaxis_quat((0, -1, 0)), name="wall_neg_y", rgba=(0.3, 0.5, 0.7, 1)))
     world.add(S.Body("pointmass_mocap", mocap=True))
     pm = world.add(S.Body("pointmass/pointmass_body", pos=(0, 0, r)))
-    pm.geoms.append(S.Geom(S.SPHERE, (r,), mass=0.1, name="pointmass/sphere"))
+    pm.geoms.append(S.Geom(S.SPHERE, (r,), mass=0.1, name="pointmass/sphere", rgba=(1, 0, 0, 0.5)))  # pointmass.py:55
     pm.joints.append(S.Joint(S.SLIDE, axis=(1, 0, 0), name="pointmass/pointmass_x"))
     pm.joints.append(S.Joint(S.SLIDE, axis=(0, 1, 0), name="pointmass/pointmass_y"))
     sc = S.Scene(world, welds=[S.Weld("pointmass_mocap", "pointmass/pointmass_body")], timestep=0.02)
@@ -112,6 +176,7 @@ def build_pointmass_reach(reward_type: str = DENSE_BIASED_NEG_DISTANCE_REWARD, m
     t.set("target_hi", (0.5 - r, 0.5 - r, r / 2))
     t.set("action_lo", [-0.05, -0.05])
     t.set("action_hi", [0.05, 0.05])
+    vis = _geom_visuals(comp) + [_marker(S.BOX, (0.04, 0.04, 0.04), (0, 1, 0, 1), "MJS_ANCHOR_TARGET", (0, 0, r / 2))]  # point_reach.py:91-93,136
     return TaskBundle(
         "point_mass_reach",
         comp,
@@ -120,6 +185,9 @@ def build_pointmass_reach(reward_type: str = DENSE_BIASED_NEG_DISTANCE_REWARD, m
         np.array([-0.05, -0.05], np.float32),
         np.array([0.05, 0.05], np.float32),
         np.float32,
+        visuals=vis,
+        cameras={"top_down": _camera((0, 0, 2.4), (1, 0, 0, 0), 30)},  # point_reach.py:22
+        image_resolution=64,
     )
 
 
@@ -139,7 +207,7 @@ def _ur5e(world: S.Body):
     overwritten to (0,0,0,-1) (robot.py:320).  Returns (wrist_3 body, actuators)."""
     J = dict(armature=0.1)
     full = (-6.28319, 6.28319)
-    col = dict(contype=_BIT_ARM, conaffinity=0)
+    col = dict(contype=_BIT_ARM, conaffinity=0, rgba=(0.7, 0.7, 0.72, 1))  # the collision primitives stand in for the visual meshes
 
     def cap(size, pos, quat=(1, 0, 0, 0), name=""):
         return S.Geom(S.CAPSULE, size, pos=pos, quat=quat, name=name, **col)
@@ -187,7 +255,8 @@ def _ur5e(world: S.Body):
 
 def _arena_plane(world: S.Body, side=3.0):
     # EmptyRobotArena(3): one ground plane (empty_robot_arena.py:18-20)
-    world.geoms.append(S.Geom(S.PLANE, (side / 2, side / 2, 0.1), name="ground", contype=_BIT_WORLD, conaffinity=_BIT_WORLD | _BIT_ARM))
+    world.geoms.append(S.Geom(S.PLANE, (side / 2, side / 2, 0.1), name="ground", contype=_BIT_WORLD, conaffinity=_BIT_WORLD | _BIT_ARM,
+                               rgba=(0.3, 0.3, 0.3, 1)))  # empty_robot_arena.py:19
 
 
 def _robot_task_common(t: MjsTask, comp: Compiled, control_dt, physics_dt, tcp_offset):
@@ -225,12 +294,13 @@ def build_planar_push(config: RobotPushConfig | None = None) -> TaskBundle:
     _arena_plane(world)
     w3, acts = _ur5e(world)
     eef = w3.add(S.Body("ur5e/cylinder_eef", pos=(0, 0.1, 0), quat=(-1, 1, 0, 0)))
-    eef.geoms.append(S.Geom(S.CYLINDER, (0.02, 0.05), pos=(0, 0, 0.051), mass=0.1, name="cylinder-EEF"))
+    eef.geoms.append(S.Geom(S.CYLINDER, (0.02, 0.05), pos=(0, 0, 0.051), mass=0.1, name="cylinder-EEF", rgba=(0.2, 0.2, 0.2, 1)))  # eef/cylinder.py:31
     R, H = 0.02, 0.019
     for i in range(cfg.n_objects):
         ob = world.add(S.Body(f"object{i}", pos=(-0.1 + 0.1 * i, -0.45, H)))
         ob.joints.append(S.Joint(S.FREE, name=f"object{i}/free"))
-        ob.geoms.append(S.Geom(S.CYLINDER, (R, H), mass=0.1, condim=4, friction=(1.0, 0.05, 0.0), name=f"object{i}/geom"))
+        ob.geoms.append(S.Geom(S.CYLINDER, (R, H), mass=0.1, condim=4, friction=(1.0, 0.05, 0.0), name=f"object{i}/geom",
+                               rgba=[(1, 0, 0, 1), (0, 0, 1, 1), (0, 1, 0, 1), (1, 1, 0, 1)][i]))  # google_block.py:12-19 colours
     sc = S.Scene(world, actuators=acts, timestep=cfg.physics_timestep, integrator=1)
     comp = compile_scene(sc)
     t = MjsTask()
@@ -258,7 +328,10 @@ def build_planar_push(config: RobotPushConfig | None = None) -> TaskBundle:
     # reachable robot workspace instead because servoL raises outside it
     t.set("action_lo", [-0.2, -0.6]); t.set("action_hi", [0.2, -0.3])
     keys = [("ur5e/tcp_position", 3), ("target_position", 2), ("block_positions", 2 * cfg.n_objects)]
-    return TaskBundle("robot_planar_push", comp, t, keys, np.array([-1, -1], np.float32), np.array([1, 1], np.float32), np.float32)
+    vis = _geom_visuals(comp) + [_marker(S.CYLINDER, (cfg.target_radius, 0.001), (1, 1, 1, 1), "MJS_ANCHOR_TARGET")]  # robot_planar_push.py:90-98
+    cams = {"front_tilted": _camera((0.0, -1.1, 0.5), (-0.7, -0.35, 0, 0.0), 70), "top_down": _camera((0.0, -0.5, 2.4), (1, 0, 0, 0), 30)}  # :42-43
+    return TaskBundle("robot_planar_push", comp, t, keys, np.array([-1, -1], np.float32), np.array([1, 1], np.float32), np.float32,
+                      visuals=vis, cameras=cams, image_resolution=96)
 
 
 def _rigid_gripper(w3: S.Body):
@@ -267,8 +340,8 @@ def _rigid_gripper(w3: S.Body):
     palm that only touches the ground plane plus a spherical fingertip at the TCP."""
     g = w3.add(S.Body("ur5e/gripper", pos=(0, 0.1, 0), quat=(-1, 1, 0, 0),
                       inertial=S.Inertial(0.9, pos=(0, 0, 0.06), diaginertia=(0.002, 0.002, 0.0008))))
-    g.geoms.append(S.Geom(S.CAPSULE, (0.03, 0.05), pos=(0, 0, 0.075), contype=_BIT_ARM, conaffinity=0, name="gripper/palm"))
-    g.geoms.append(S.Geom(S.SPHERE, (0.015,), pos=(0, 0, 0.159), name="gripper/fingertip"))
+    g.geoms.append(S.Geom(S.CAPSULE, (0.03, 0.05), pos=(0, 0, 0.075), contype=_BIT_ARM, conaffinity=0, name="gripper/palm", rgba=(0.1, 0.1, 0.1, 1)))
+    g.geoms.append(S.Geom(S.SPHERE, (0.015,), pos=(0, 0, 0.159), name="gripper/fingertip", rgba=(0.1, 0.1, 0.1, 1)))
     return g
 
 
@@ -305,7 +378,9 @@ def build_robot_reach(config: RobotReachConfig | None = None) -> TaskBundle:
     t.set("target_lo", lo); t.set("target_hi", hi)
     t.set("action_lo", lo); t.set("action_hi", hi)
     keys = [("ur5e/tcp_position", 3), ("target_position", 3)]
-    return TaskBundle("robot_reach", comp, t, keys, np.array(lo, np.float64), np.array(hi, np.float64), np.float64)
+    vis = _geom_visuals(comp) + [_marker(S.SPHERE, (0.01,), (1, 1, 1, 1), "MJS_ANCHOR_TARGET")]  # robot_reach.py:97-104 (target_radius)
+    return TaskBundle("robot_reach", comp, t, keys, np.array(lo, np.float64), np.array(hi, np.float64), np.float64,
+                      visuals=vis, cameras={"front_tilted": _camera((0.0, -1.1, 0.5), (-0.7, -0.35, 0, 0.0), 70)}, image_resolution=96)  # :52
 
 
 def build_push_button(max_steps: int = 100, button_disturbances: bool = False) -> TaskBundle:
@@ -317,8 +392,8 @@ def build_push_button(max_steps: int = 100, button_disturbances: bool = False) -
     w3, acts = _ur5e(world)
     _rigid_gripper(w3)
     sw = world.add(S.Body("switch", pos=(0.0, -0.45, 0.0)))
-    sw.geoms.append(S.Geom(S.BOX, (0.025, 0.025, 0.025), pos=(0, 0, 0.025), name="switch/box"))
-    sw.geoms.append(S.Geom(S.CYLINDER, (0.02, 0.02), pos=(0, 0, 0.05), name="switch/button"))
+    sw.geoms.append(S.Geom(S.BOX, (0.025, 0.025, 0.025), pos=(0, 0, 0.025), name="switch/box", rgba=(1, 1, 1, 1)))        # switch.py:24-29
+    sw.geoms.append(S.Geom(S.CYLINDER, (0.02, 0.02), pos=(0, 0, 0.05), name="switch/button", rgba=(1, 0, 0, 1)))        # switch.py:30-36
     sw.sites.append(S.Site("switch/button_site", pos=(0, 0, 0.05)))
     sc = S.Scene(world, actuators=acts, timestep=0.005, integrator=1, ovr_body="switch",
                  touch_site="switch/button_site", touch_size=(0.02 * 1.01, 0.02 * 1.01))
@@ -340,4 +415,12 @@ def build_push_button(max_steps: int = 100, button_disturbances: bool = False) -
     # synthetic rollouts: q_now +- 0.05 rad handled on device; box kept for the gripper dof
     t.set("action_lo", [-0.05] * 6 + [0.0]); t.set("action_hi", [0.05] * 6 + [0.085])
     keys = [("ur5e/joint_configuration", 6), ("unnamed_model/position", 3), ("unnamed_model/active", 1)]
-    return TaskBundle("robot_push_button", comp, t, keys, np.array([-3.14] * 6 + [0.0]), np.array([3.14] * 6 + [0.085]), np.float64)
+    vis = _geom_visuals(comp, active={"switch/button": (0, 1, 0, 1)})  # switch.py:59: green while active
+    # scene camera and the wrist camera riding on the flange (robot_push_button.py:51-55,87-96); the flange frame is the
+    # frame of the gripper palm geom's body up to the geom's own offset, so the wrist camera is anchored to wrist_3's geom
+    cams = {"scene": _camera((0.0, -1.7, 0.7), (-0.7, -0.35, 0, 0.0), 70)}
+    gw = comp.geom_id["ur5e/w3_col"]  # cylinder at (0, 0.08, 0), quat (1, 1, 0, 0) in wrist_3; flange site at (0, 0.1, 0), quat (-1, 1, 0, 0)
+    wp, wq = _in_geom_frame((0, 0.08, 0), (1, 1, 0, 0), (0, 0.1, 0), (-1, 1, 0, 0), (0.0, 0.05, 0.0), (0.0, 0.0, 0.999, 0.04))
+    cams["wrist"] = _camera(wp, wq, 42, geom=gw)
+    return TaskBundle("robot_push_button", comp, t, keys, np.array([-3.14] * 6 + [0.0]), np.array([3.14] * 6 + [0.085]), np.float64,
+                      visuals=vis, cameras=cams, image_resolution=96)

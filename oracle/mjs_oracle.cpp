@@ -1466,6 +1466,16 @@ void oracle_control_step(const MjsModel* m, const MjsTask* t, MjsEnvState* state
   for (int e = 0; e < n; e++) control_step(m, t, states + e, actions + (size_t)e * t->action_dim, outs + e, tol_scale, flops);
 }
 
+// world poses of every model geom at the given state (mj_kinematics): xpos[ngeom][3], xmat[ngeom][9].  Feeds the numpy
+// restatement of the ray caster (oracle/render_ref.py).
+void oracle_geom_poses(const MjsModel* m, const MjsEnvState* state, double* xpos, double* xmat) {
+  static thread_local Data d;
+  MjsEnvState s = *state;
+  step1(m, &s, &d);
+  std::memcpy(xpos, d.geom_xpos, sizeof(double) * 3 * m->ngeom);
+  std::memcpy(xmat, d.geom_xmat, sizeof(double) * 9 * m->ngeom);
+}
+
 // oracle_control_step with the button-disturbance draw of every env supplied by the caller: u[n] in [0, 1)
 void oracle_control_step_disturb(const MjsModel* m, const MjsTask* t, MjsEnvState* states, const double* actions, MjsStepOut* outs, int n, double tol_scale, const double* u) {
   for (int e = 0; e < n; e++) {

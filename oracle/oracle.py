@@ -112,6 +112,13 @@ class OracleEnvs:
         flags = np.array([[o.terminated, o.truncated, o.success, o.done] for o in self.outs], dtype=np.uint8)
         return obs, rew, disc, flags
 
+    def geom_poses(self, e: int):
+        """world pose of every model geom of env e: (xpos [ngeom, 3], xmat [ngeom, 9])"""
+        ng = self.model.ngeom
+        xpos, xmat = np.zeros((ng, 3)), np.zeros((ng, 9))
+        lib().oracle_geom_poses(ctypes.byref(self.model), ctypes.byref(self.states[e]), _dp(xpos), _dp(xmat))
+        return xpos, xmat
+
     def ncon(self, e: int) -> int:
         return lib().oracle_ncon(ctypes.byref(self.model), ctypes.byref(self.states[e]))
 
