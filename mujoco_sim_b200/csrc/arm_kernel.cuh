@@ -17,6 +17,7 @@
 // state integration), see DESIGN.md.
 #pragma once
 #include "arm_model.cuh"
+#include "../../include/mjs_convex.h"
 
 #define FULLMASK 0xffffffffu
 // warps per lock-step group (must divide the warps per block of the step kernel).  Measured on B200,
@@ -84,6 +85,9 @@ struct WarpMem {
   int novote;   // lock-step without the Newton loop: the stages before the solve stay aligned, the data-dependent iterations run free
   int coup;     // bit b: the arm block shares a contact with prop b
   int objcoup;  // non-zero: two props share a contact (dense factorisation path)
+#ifdef MJS_CONVEX_COUNT
+  int ncvx, ncvx_hit;  // profiling build: calls of the general convex routine / calls that found a contact, per control step
+#endif
 #ifdef MJS_STAGE_CLOCKS
   long long clk[MJS_NCLK];  // profiling build: cycles per stage, accumulated by lane 0
 #endif
@@ -215,6 +219,83 @@ __device__ __forceinline__ void spi_mul(real* f, const real* I, const real* v) {
   f[0] = I[4] * v[0] + I[7] * v[1] + I[8] * v[2] + t[0];
   f[1] = I[7] * v[0] + I[5] * v[1] + I[9] * v[2] + t[1];
   f[2] = I[8] * v[0] + I[9] * v[1] + I[6] * v[2] + t[2];
+}
+
+// General convex pair (mjc_Convex restated by include/mjs_convex.h, the same source the oracle compiles): MPR penetration,
+// one contact.  Deliberately not inlined: it runs only for the rare pairs without an analytic routine (a prop's cap against
+// another prop or the pusher, cylinder x box, capsule x cylinder / box) and must stay out of the substep's hot code.
+// Cheap, sound rejection before the general convex routine: two cylinders are disjoint if their projections on some axis
+// do not overlap (separating-axis test on four candidate axes: both cylinder axes, their cross product and `extra`, the
+// direction between the closest points of the axis segments or between the centres).  Extent of a cylinder (radius r,
+// half-height h, axis a) along a unit axis d: h |a.d| + r sqrt(1 - (a.d)^2).  The oracle runs the same test (cyl_separated).
+template <typename real>
+__device__ __forceinline__ bool cyl_separated(const real* dif, const real* a1, real r1, real h1, const real* a2, real r2, real h2, const real* extra) {
+  real cx[3];
+  cross3(cx, a1, a2);
+  bool sep = false;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    real d[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) d[i] = k == 0 ? a1[i] : k == 1 ? a2[i] : k == 2 ? cx[i] : extra[i];
+    real n2 = dot3(d, d);
+    if (n2 > (real)1e-20) {
+      real inv = rsqrt_r<real>(n2);
+      real c1 = dot3(a1, d) * inv, c2 = dot3(a2, d) * inv;
+      real e1 = h1 * fabs(c1) + r1 * sqrt(fmax((real)0, 1 - c1 * c1)), e2 = h2 * fabs(c2) + r2 * sqrt(fmax((real)0, 1 - c2 * c2));
+      if (fabs(dot3(dif, d)) * inv > e1 + e2) sep = true;
+    }
+  }
+  return sep;
+}
+
+// separating axis of this lane's pair found by the last miss of the general convex routine (zero: none); lives in the pair
+// lane's registers for the rest of the control step
+template <typename real>
+struct SepAxis { float v[3]; };  // FP32 on purpose: any axis gives a sound test, and it lives in registers across the whole substep
+template <typename real>
+__device__ __forceinline__ bool cyl_axis_separates(const real* dif, const real* a1, real r1, real h1, const real* a2, real r2, real h2, const real* d) {
+  real n2 = dot3(d, d);
+  if (!(n2 > (real)1e-20)) return false;
+  real inv = rsqrt_r<real>(n2);
+  real c1 = dot3(a1, d) * inv, c2 = dot3(a2, d) * inv;
+  real e1 = h1 * fabs(c1) + r1 * sqrt(fmax((real)0, 1 - c1 * c1)), e2 = h2 * fabs(c2) + r2 * sqrt(fmax((real)0, 1 - c2 * c2));
+  return fabs(dot3(dif, d)) * inv > (e1 + e2) * (1 + (real)1e-6);  // the cached axis is FP32: keep a relative safety margin
+}
+
+template <typename real>
+struct ConvexHit { real dist, n[3], p[3]; int hit; };
+// Arguments are geom indices and shared-memory poses only, the result comes back by value: nothing of the caller's register
+// state (cd / cp / nrm / sizes in collide) becomes addressable, so the hot path keeps its registers.
+#ifndef MJS_CONVEX_INLINE
+#define MJS_CONVEX_INLINE __forceinline__   // one call site, inside the non-inlined convex_fixup
+#endif
+// The portal search runs in the kernel's own precision (FP64 for precision f64: parity with the oracle to rounding).  One lane
+// walks a dependent chain of ~15 support evaluations while its warp -- and, through the substep barrier, its lock-step
+// group -- waits: ~4 substeps of SM time per call in FP64 (profiles/r2/convex_pairs.txt).  Most calls are persistent
+// near-misses of resting props, so the separating axis of a miss is cached per pair lane for the rest of the control step
+// (collide, `sep`) and tested first: sound, and 8x fewer calls.
+template <typename real>
+__device__ MJS_CONVEX_INLINE ConvexHit<real> convex_pair_dev(int g1, int g2, const real* p1, const real* m1, const real* p2, const real* m2) {
+  MjsShape<real> A, B;
+  A.type = GM().geom_type[g1]; B.type = GM().geom_type[g2];
+#pragma unroll
+  for (int k = 0; k < 3; k++) { A.size[k] = GM().geom_size[g1][k]; A.pos[k] = 0; B.size[k] = GM().geom_size[g2][k]; B.pos[k] = p2[k] - p1[k]; }
+#pragma unroll
+  for (int k = 0; k < 9; k++) { A.mat[k] = m1[k]; B.mat[k] = m2[k]; }
+  ConvexHit<real> r;
+  real depth = 0;
+#if defined(MJS_CONVEX_MODE) && MJS_CONVEX_MODE == 1   // A/B build: the call without the algorithm
+  r.hit = 0; r.n[0] = r.n[1] = r.n[2] = 0; r.p[0] = r.p[1] = r.p[2] = 0; r.dist = A.size[0] + B.size[0]; return r;
+#endif
+  r.hit = mjs_mpr_penetration<real>(A, B, &depth, r.n, r.p);  // on a miss r.n is the separating axis found (or zero)
+#if defined(MJS_CONVEX_MODE) && MJS_CONVEX_MODE == 2   // A/B build: the algorithm runs, its contact is dropped
+  r.hit = 0;
+#endif
+  r.dist = -depth;
+#pragma unroll
+  for (int k = 0; k < 3; k++) r.p[k] += p1[k];
+  return r;
 }
 
 template <typename real, int NOBJ>
@@ -494,7 +575,8 @@ struct ArmEngine {
     _Pragma("unroll") for (int _s = 0; _s < 4; _s++)                                                  \
       if (_s == (N)) { cd[_s] = _d; cp[_s][0] = _x; cp[_s][1] = _y; cp[_s][2] = _z; }                 \
   } while (0)
-  __device__ static void collide(const AM& A, WM& W, int lane) {
+  __device__ static void collide(const AM& A, WM& W, int lane, const SepAxis<real>& sep, bool& cvx) {
+    cvx = false;
     int n = 0;
     // (zero-initialised on purpose: ptxas keeps the arrays in registers only when every slot has a definite value)
     real cd[4] = {0, 0, 0, 0}, cp[4][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}, {0, 0, 0}}, nrm[3] = {0, 0, 1}, yh[3] = {0, 0, 0};
@@ -591,6 +673,7 @@ struct ArmEngine {
           real q1[3] = {p1[0], p1[1], p1[2]}, q2[3] = {p2[0], p2[1], p2[2]}, r1 = 0, r2 = 0;
           real s1[3] = {GM().geom_size[g1][0], GM().geom_size[g1][1], GM().geom_size[g1][2]};
           int mode = 1;  // 1: spheres, 2: explicit result in (cd[0], nrm, cp[0]), 0: nothing
+          bool needs_convex = false;  // the pair goes to the general convex routine (rare; called once, below)
           if (t1 == MJS_GEOM_SPHERE && t2 == MJS_GEOM_SPHERE) { r1 = s1[0]; r2 = s2[0]; }
           else if (t1 == MJS_GEOM_SPHERE && t2 == MJS_GEOM_CAPSULE) {
             real ax[3] = {m2[2], m2[5], m2[8]}, vv[3] = {-dif[0], -dif[1], -dif[2]};
@@ -599,11 +682,13 @@ struct ArmEngine {
             r1 = s1[0]; r2 = s2[0];
           } else if (t1 == MJS_GEOM_CYLINDER && t2 == MJS_GEOM_CYLINDER) {
             real a1[3] = {m1[2], m1[5], m1[8]}, a2[3] = {m2[2], m2[5], m2[8]};
+            const real sepd[3] = {(real)sep.v[0], (real)sep.v[1], (real)sep.v[2]};
             real tc = dot3(a1, dif), ta = fabs(dot3(a1, a2) * s2[1]);
             real lo = fmax(-s1[1], tc - ta), hi = fmin(s1[1], tc + ta);
             if (lo > hi) {
-              real radial[3] = {dif[0] - a1[0] * tc, dif[1] - a1[1] * tc, dif[2] - a1[2] * tc};
-              if (lo - hi <= margin && sqrt(dot3(radial, radial)) < s1[0] + s2[0]) atomicOr(&W.status, MJS_STATUS_UNSUPPORTED_PAIR);
+              // no axial overlap of the axis segments: only a cap configuration can touch -> general convex routine
+              needs_convex = !cyl_separated<real>(dif, a1, s1[0], s1[1], a2, s2[0], s2[1], dif) &&
+                             !cyl_axis_separates<real>(dif, a1, s1[0], s1[1], a2, s2[0], s2[1], sepd);
               mode = 0;
             } else {
               real sm = (real)0.5 * (lo + hi);
@@ -612,6 +697,19 @@ struct ArmEngine {
               real u = fmin(fmax(dot3(a2, w3), -s2[1]), s2[1]);
               for (int k = 0; k < 3; k++) q2[k] = p2[k] + a2[k] * u;
               r1 = s1[0]; r2 = s2[0];
+              // side-side is only right while the radial direction is the axis of least penetration (oracle cylinder_cylinder)
+              real dq[3] = {q2[0] - q1[0], q2[1] - q1[1], q2[2] - q1[2]};
+              real radial_pen = r1 + r2 - sqrt(dot3(dq, dq));
+              if (radial_pen > 0) {  // (rare: only for pairs in contact)
+                // extent of cylinder 2 along axis 1 (axis segment + rim), so that a prop lying on its side still overlaps axially
+                real ca = dot3(a1, a2), ext = fabs(ca) * s2[1] + s2[0] * sqrt(fmax((real)0, 1 - ca * ca));
+                real axial_pen = fmin(s1[1], tc + ext) - fmax(-s1[1], tc - ext);
+                if (axial_pen < radial_pen) {  // cap-cap / cap-rim / cap-side: the general convex routine
+                  needs_convex = !cyl_separated<real>(dif, a1, s1[0], s1[1], a2, s2[0], s2[1], dq) &&
+                                 !cyl_axis_separates<real>(dif, a1, s1[0], s1[1], a2, s2[0], s2[1], sepd);
+                  mode = 0;
+                }
+              }
             }
           } else if (t1 == MJS_GEOM_SPHERE && t2 == MJS_GEOM_CYLINDER) {
             real ax[3] = {m2[2], m2[5], m2[8]}, vv[3] = {-dif[0], -dif[1], -dif[2]};
@@ -654,10 +752,50 @@ struct ArmEngine {
               mode = 2; cd[0] = -bd - r1;
               for (int k = 0; k < 3; k++) cp[0][k] = p1[k] + nrm[k] * (r1 + (real)0.5 * cd[0]);
             }
+          } else if (t1 == MJS_GEOM_CAPSULE && t2 == MJS_GEOM_CAPSULE) {
+            // mjc_CapsuleCapsule (oracle capsule_capsule): closest points of the two axis segments; parallel axes give the
+            // two end-point tests of segment 1
+            real a1[3] = {m1[2], m1[5], m1[8]}, a2[3] = {m2[2], m2[5], m2[8]}, df[3] = {-dif[0], -dif[1], -dif[2]};
+            real ma = dot3(a1, a1), mb = -dot3(a1, a2), mc = dot3(a2, a2), u = -dot3(a1, df), v = dot3(a2, df);
+            real det = ma * mc - mb * mb;
+            r1 = s1[0]; r2 = s2[0];
+            if (fabs(det) >= (real)MJS_MINVAL) {
+              real x1 = (mc * u - mb * v) / det, x2 = (ma * v - mb * u) / det;
+              if (x1 > s1[1]) { x1 = s1[1]; x2 = (v - mb * s1[1]) / mc; }
+              else if (x1 < -s1[1]) { x1 = -s1[1]; x2 = (v + mb * s1[1]) / mc; }
+              if (x2 > s2[1]) { x2 = s2[1]; x1 = (u - mb * s2[1]) / ma; }
+              else if (x2 < -s2[1]) { x2 = -s2[1]; x1 = (u + mb * s2[1]) / ma; }
+              x1 = fmin(fmax(x1, -s1[1]), s1[1]);
+              x2 = fmin(fmax(x2, -s2[1]), s2[1]);
+              for (int k = 0; k < 3; k++) { q1[k] = p1[k] + a1[k] * x1; q2[k] = p2[k] + a2[k] * x2; }
+            } else {
+              mode = 0;
+#pragma unroll
+              for (int e2 = 0; e2 < 2; e2++) {
+                real x1 = e2 == 0 ? s1[1] : -s1[1];
+                real x2 = fmin(fmax((v - mb * x1) / mc, -s2[1]), s2[1]);
+                real qa[3], qb[3], d3[3];
+                for (int k = 0; k < 3; k++) { qa[k] = p1[k] + a1[k] * x1; qb[k] = p2[k] + a2[k] * x2; d3[k] = qb[k] - qa[k]; }
+                real len = sqrt(dot3(d3, d3)), dist = len - r1 - r2;
+                if (dist <= margin) {
+                  if (len < (real)MJS_MINVAL) { d3[0] = 1; d3[1] = 0; d3[2] = 0; } else { d3[0] /= len; d3[1] /= len; d3[2] /= len; }
+                  for (int k = 0; k < 3; k++) nrm[k] = d3[k];  // parallel axes: both end-point contacts share the normal
+                  MJS_CPUT(n, dist, qa[0] + d3[0] * (r1 + (real)0.5 * dist), qa[1] + d3[1] * (r1 + (real)0.5 * dist), qa[2] + d3[2] * (r1 + (real)0.5 * dist));
+                  n++;
+                }
+              }
+            }
+          } else if ((t1 == MJS_GEOM_CAPSULE || t1 == MJS_GEOM_CYLINDER) && (t2 == MJS_GEOM_CYLINDER || t2 == MJS_GEOM_BOX)) {
+            needs_convex = true;
+            mode = 0;
           } else {
             atomicOr(&W.status, MJS_STATUS_UNSUPPORTED_PAIR);
             mode = 0;
           }
+          // The general convex routine is NOT called from here: a call inside this function costs the hot path registers
+          // (measured: 2.33 -> 1.85 M env-steps/s with the call here, whatever the call rate).  The lane only reports the
+          // pair; substep() runs convex_fixup() after collide, when the narrowphase's registers are dead.
+          if (needs_convex) cvx = true;
           if (mode == 1) {
             real d3[3] = {q2[0] - q1[0], q2[1] - q1[1], q2[2] - q1[2]};
             real len = sqrt(dot3(d3, d3)), dist = len - r1 - r2;
@@ -1455,15 +1593,50 @@ struct ArmEngine {
     __syncwarp();
   }
 
+  // Pairs that collide() handed to the general convex routine (lane = pair): MPR penetration, the contact appended to the
+  // warp's contact list, the separating axis of a miss returned for the next substep.  Runs between collide and make_rows.
+  __device__ static __noinline__ SepAxis<real> convex_fixup(WM* Wp, int lane, bool cvx, SepAxis<real> sep) {
+    WM& W = *Wp;
+    if (cvx) {
+      const int g1 = GM().pair_g1[lane], g2 = GM().pair_g2[lane];
+#if defined(MJS_CONVEX_MODE) && MJS_CONVEX_MODE == 0   // A/B build: the pre-MPR behaviour (status bit instead of a contact)
+      atomicOr(&W.status, MJS_STATUS_UNSUPPORTED_PAIR);
+#else
+#ifdef MJS_CONVEX_COUNT
+      atomicAdd(&W.ncvx, 1);
+#endif
+      const ConvexHit<real> ch = convex_pair_dev<real>(g1, g2, W.gpos[g1], W.gmat[g1], W.gpos[g2], W.gmat[g2]);
+      sep.v[0] = ch.hit ? 0.f : (float)ch.n[0]; sep.v[1] = ch.hit ? 0.f : (float)ch.n[1]; sep.v[2] = ch.hit ? 0.f : (float)ch.n[2];
+      if (ch.hit && ch.dist < GM().pair_incl[lane]) {  // mj_collision: contacts with dist >= margin - gap produce no rows
+#ifdef MJS_CONVEX_COUNT
+        atomicAdd(&W.ncvx_hit, 1);
+#endif
+        const int c = atomicAdd(&W.ncon, 1);
+        if (c < ARM_MAXC) {
+          W.craw[0][c] = ch.dist;
+          W.craw[1][c] = ch.p[0]; W.craw[2][c] = ch.p[1]; W.craw[3][c] = ch.p[2];
+          W.craw[4][c] = ch.n[0]; W.craw[5][c] = ch.n[1]; W.craw[6][c] = ch.n[2];
+          W.craw[7][c] = 0; W.craw[8][c] = 0; W.craw[9][c] = 0;
+          W.cpair[c] = lane;
+        } else atomicOr(&W.status, MJS_STATUS_CONTACT_OVERFLOW);
+      }
+#endif
+    }
+    __syncwarp();
+    if (lane == 0 && W.ncon > ARM_MAXC) W.ncon = ARM_MAXC;
+    __syncwarp();
+    return sep;
+  }
+
   // ------------------------------------------------ one physics substep (legacy_step)
-  struct SubRes { real a_i; double time; real touch; int niter; };
+  struct SubRes { real a_i; double time; real touch; int niter; SepAxis<real> sep; };
 
   // One physics step for the current (qpos, qvel, ctrl): mj_step1 (kinematics ..
   // constraint rows) followed by mj_step2 (solve, touch sensor, integrate).  The
   // composer loop's "step2 then step1" order is the same sequence seen from the
   // state's point of view (ArmTask::control_step).  Deliberately NOT inlined:
   // one copy of the heavy code keeps the instruction footprint inside the i-cache.
-  __device__ static __noinline__ SubRes substep(WM* Wp, int lane, real a_i, double time, int do_integrate) {
+  __device__ static __noinline__ SubRes substep(WM* Wp, int lane, real a_i, double time, int do_integrate, SepAxis<real> sep = SepAxis<real>{{0, 0, 0}}) {
     const AM& A = cmodel<real>();
     WM& W = *Wp;
     ConReg C;
@@ -1492,7 +1665,9 @@ struct ArmEngine {
     bool clamped = dynamics(A, W, lane);
     STAGE_CLK(W, 1, tclk);
     stage_sync(W, 3);
-    collide(A, W, lane);
+    bool cvx;
+    collide(A, W, lane, sep, cvx);
+    if (__any_sync(FULLMASK, cvx)) sep = convex_fixup(&W, lane, cvx, sep);  // rare: pairs without an analytic routine (cap contacts)
     STAGE_CLK(W, 2, tclk);
 #endif
     stage_sync(W, 3);
@@ -1508,11 +1683,12 @@ struct ArmEngine {
     STAGE_CLK(W, 9, tclk);
     r.a_i = a_i;
     r.time = time;
+    r.sep = sep;
     return r;
   }
   __device__ static __noinline__ void kinematics_only(WM* Wp, int lane) { kinematics(cmodel<real>(), *Wp, lane); }
   __device__ static __noinline__ bool dynamics_only(WM* Wp, int lane) { return dynamics(cmodel<real>(), *Wp, lane); }
-  __device__ static __noinline__ void collide_only(WM* Wp, int lane) { collide(cmodel<real>(), *Wp, lane); }
+  __device__ static __noinline__ void collide_only(WM* Wp, int lane) { SepAxis<real> sep = {{0, 0, 0}}; bool cvx; collide(cmodel<real>(), *Wp, lane, sep, cvx); }
 };
 
 // ===================================================================== analytic UR IK
@@ -1690,6 +1866,9 @@ struct ArmTask {
     T.step = si[L::I_STEP]; T.traj = si[L::I_TRAJ]; T.swa = si[L::I_SWA]; T.swp = si[L::I_SWP]; T.swc = si[L::I_SWC];
     T.status = si[L::I_STATUS]; T.episode = si[L::I_EPISODE]; T.len = si[L::I_LEN];
     if (lane == 0) { W.status = 0; W.sync = sync & 7; W.novote = (sync >> 3) & 1; W.period = 1 + ((sync >> 4) & 15); }
+#ifdef MJS_CONVEX_COUNT
+    if (lane == 0) { W.ncvx = 0; W.ncvx_hit = 0; }
+#endif
 #ifdef MJS_STAGE_CLOCKS
     if (lane < MJS_NCLK) W.clk[lane] = 0;
 #endif
@@ -1826,10 +2005,11 @@ struct ArmTask {
     }
     int nit_sum = 0, nit_max = 0;
     o.h4 = o.h8 = o.h16 = o.h32 = 0;
+    SepAxis<real> sep = {{0, 0, 0}};  // per pair lane: separating axis cached across the substeps of this control step
     for (int k = 0; k < A.n_sub; k++) {
       before_substep(A, W, lane, T);
-      typename E::SubRes so = E::substep(&W, lane, a_i, T.time, (k % W.period) ? 3 : 1);  // bit 1: skip the substep-start barrier
-      a_i = so.a_i; T.time = so.time;
+      typename E::SubRes so = E::substep(&W, lane, a_i, T.time, (k % W.period) ? 3 : 1, sep);  // bit 1: skip the substep-start barrier
+      a_i = so.a_i; T.time = so.time; sep = so.sep;
       nit_sum += so.niter; nit_max = so.niter > nit_max ? so.niter : nit_max;
 #ifdef MJS_NIT_HIST
       o.h4 += so.niter >= 3; o.h8 += so.niter >= 6; o.h16 += so.niter >= 12; o.h32 += so.niter >= 30;
@@ -1849,6 +2029,11 @@ struct ArmTask {
     bool bad = false;
     if (lane < NV) bad = !(isfinite(W.qvel[lane]) && isfinite(W.qpos[lane]));
     if (__any_sync(FULLMASK, bad)) { T.status |= MJS_STATUS_NAN; o.done = 1; o.truncated = 1; o.terminated = 0; }
+    // A geom pair the narrowphase has no routine for (or more contacts than the solver holds) came within margin during this
+    // step: the bodies may interpenetrate from here on, so the episode is cut (truncated, status bit kept) instead of
+    // returning rewards of a scene that is no longer simulated faithfully.
+    __syncwarp();
+    if (W.status & (MJS_STATUS_UNSUPPORTED_PAIR | MJS_STATUS_CONTACT_OVERFLOW)) { o.done = 1; o.truncated = 1; o.terminated = 0; }
   }
 
   // Scripted demonstrators: robot_reach.py:222-253, robot_push_button.py:231-300.
@@ -2118,6 +2303,9 @@ __device__ __noinline__ void arm_step_env(const ArmModel<real>& A, WarpMem<real,
     // SURVEY.md 8e) instead of two same-address global atomics per env and launch
     if (io.stats) {  // solver effort: env-substeps and Newton iterations (mjs_stats slots 6 and 7)
       atomicAdd(bstat + 6, (double)A.n_sub); atomicAdd(bstat + 7, (double)o.nit_sum);
+#ifdef MJS_CONVEX_COUNT
+      atomicAdd(bstat + 3, (double)W.ncvx); atomicAdd(bstat + 5, (double)W.ncvx_hit);
+#endif
 #ifdef MJS_NIT_HIST
       atomicAdd(bstat + 2, (double)o.h4); atomicAdd(bstat + 3, (double)o.h8); atomicAdd(bstat + 4, (double)o.h16); atomicAdd(bstat + 5, (double)o.h32);
 #endif

@@ -198,6 +198,7 @@ def build_pointmass_reach(reward_type: str = DENSE_BIASED_NEG_DISTANCE_REWARD, m
 # non-adjacent arm x arm pairs, which never touch in these workspaces.
 _BIT_WORLD = 1
 _BIT_ARM = 2
+_BIT_OBST = 4  # test obstacles (capsules) that only the arm's link CAPSULES meet
 
 
 def _ur5e(world: S.Body):
@@ -210,7 +211,7 @@ def _ur5e(world: S.Body):
     col = dict(contype=_BIT_ARM, conaffinity=0, rgba=(0.7, 0.7, 0.72, 1))  # the collision primitives stand in for the visual meshes
 
     def cap(size, pos, quat=(1, 0, 0, 0), name=""):
-        return S.Geom(S.CAPSULE, size, pos=pos, quat=quat, name=name, **col)
+        return S.Geom(S.CAPSULE, size, pos=pos, quat=quat, name=name, **{**col, "contype": _BIT_ARM | _BIT_OBST})
 
     base = world.add(S.Body("ur5e/base", quat=(0, 0, 0, -1), gravcomp=1.0,
                             inertial=S.Inertial(4.0, diaginertia=(0.00443333156, 0.00443333156, 0.0072))))
@@ -356,10 +357,15 @@ class RobotReachConfig:
     goal_distance_threshold: float = 0.02
 
 
-def build_robot_reach(config: RobotReachConfig | None = None) -> TaskBundle:
+def build_robot_reach(config: RobotReachConfig | None = None, obstacle: dict | None = None) -> TaskBundle:
+    """RobotReachTask scene (robot_reach.py:85-132).  `obstacle` (not in the reference; used by the collision parity tests):
+    a static capsule in the world that the arm's link capsules collide with, dict(size=(r, hh), pos=..., quat=...)."""
     cfg = config or RobotReachConfig()
     world = S.Body("world")
     _arena_plane(world)
+    if obstacle:
+        world.geoms.append(S.Geom(S.CAPSULE, obstacle["size"], pos=obstacle["pos"], quat=obstacle.get("quat", (1, 0, 0, 0)), name="obstacle",
+                                  contype=_BIT_WORLD, conaffinity=_BIT_OBST, rgba=(0.8, 0.4, 0.1, 1)))
     w3, acts = _ur5e(world)
     _rigid_gripper(w3)
     sc = S.Scene(world, actuators=acts, timestep=cfg.physics_timestep, integrator=1)

@@ -20,10 +20,12 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
 #include "../include/mjs_model.h"
+#include "../include/mjs_convex.h"
 
 namespace {
 
@@ -606,6 +608,25 @@ int capsule_capsule(const double* p1, const double* m1, const double* s1, const 
   return n;
 }
 
+// Sound rejection before the general convex routine (same test as cyl_separated in arm_kernel.cuh): separating-axis test of
+// two cylinders on both axes, their cross product and `extra`.
+bool cyl_separated(const double* dif, const double* a1, double r1, double h1, const double* a2, double r2, double h2, const double* extra) {
+  double cx[3];
+  cross3(cx, a1, a2);
+  bool sep = false;
+  for (int k = 0; k < 4; k++) {
+    const double* d = k == 0 ? a1 : k == 1 ? a2 : k == 2 ? cx : extra;
+    double n2 = dot3(d, d);
+    if (n2 > 1e-20) {
+      double inv = 1.0 / std::sqrt(n2);
+      double c1 = dot3(a1, d) * inv, c2 = dot3(a2, d) * inv;
+      double e1 = h1 * std::fabs(c1) + r1 * std::sqrt(std::max(0.0, 1 - c1 * c1)), e2 = h2 * std::fabs(c2) + r2 * std::sqrt(std::max(0.0, 1 - c2 * c2));
+      if (std::fabs(dot3(dif, d)) * inv > e1 + e2) sep = true;
+    }
+  }
+  return sep;
+}
+
 // Cylinder x cylinder, SIDE-SIDE contact only (own analytic routine; MuJoCo
 // routes this pair through its iterative convex solver).  One
 // contact at the midpoint of the axial overlap; continuous in the tilt angle.
@@ -621,8 +642,11 @@ int cylinder_cylinder(const double* p1, const double* m1, const double* s1, cons
     double radial[3];
     set3(radial, dif);
     addscl3(radial, a1, -tc);
-    if (gap <= margin && norm3(radial) < s1[0] + s2[0]) return -1;
-    return 0;
+    (void)gap; (void)radial;
+    // only a cap configuration can touch: the caller asks the general convex routine unless an axis separates the cylinders
+    { bool sp = cyl_separated(dif, a1, s1[0], s1[1], a2, s2[0], s2[1], dif);
+      if (getenv("ORACLE_CVX_LOG") && !sp) fprintf(stderr, "CVX A h1 %.3f h2 %.3f cos %.3f tc %.4f dist %.4f z1 %.3f z2 %.3f\n", s1[1], s2[1], dot3(a1, a2), tc, norm3(dif), p1[2], p2[2]);
+      return sp ? 0 : -1; }
   }
   double sm = 0.5 * (lo + hi);
   double q1[3], q2[3], w[3];
@@ -630,7 +654,39 @@ int cylinder_cylinder(const double* p1, const double* m1, const double* s1, cons
   sub3(w, q1, p2);
   double u = std::min(std::max(dot3(a2, w), -s2[1]), s2[1]);
   set3(q2, p2); addscl3(q2, a2, u);
+  // The side-side contact is only the right answer while the radial direction is the axis of least penetration.  When the
+  // axial overlap is the smaller one (a prop resting on another prop's cap) the true contact is cap-cap / cap-rim: unsupported.
+  double dq[3];
+  sub3(dq, q2, q1);
+  double radial_pen = s1[0] + s2[0] - norm3(dq);
+  // extent of cylinder 2 along axis 1 (axis segment + rim), so that a prop lying on its side still overlaps axially
+  double ca = dot3(a1, a2), ext = std::fabs(ca) * s2[1] + s2[0] * std::sqrt(std::max(0.0, 1.0 - ca * ca));
+  double axial_pen = std::min(s1[1], tc + ext) - std::max(-s1[1], tc - ext);
+  if (radial_pen > 0 && axial_pen < radial_pen) {
+    bool sp = cyl_separated(dif, a1, s1[0], s1[1], a2, s2[0], s2[1], dq);
+    if (getenv("ORACLE_CVX_LOG") && !sp) fprintf(stderr, "CVX B h1 %.3f h2 %.3f cos %.3f tc %.4f dist %.4f z1 %.3f z2 %.3f axpen %.4f radpen %.4f\n", s1[1], s2[1], dot3(a1, a2), tc, norm3(dif), p1[2], p2[2], axial_pen, radial_pen);
+    return sp ? 0 : -1;
+  }
   return sphere_sphere_raw(q1, s1[0], q2, s2[0], margin, c);
+}
+
+// General convex pair (mjc_Convex): MPR penetration of the two primitives, one contact.  Used for the pairs MuJoCo has no
+// analytic routine for (cylinder x box, capsule x cylinder, capsule x box here) and for the cap configurations of
+// cylinder x cylinder that the side-side routine above declines.  margin > 0 is not supported by this restatement (the
+// scenes use margin 0): shapes that do not intersect give no contact.
+int convex_pair(int t1, const double* p1, const double* m1, const double* s1, int t2, const double* p2, const double* m2, const double* s2, RawCon* c) {
+  MjsShape<double> A, B;
+  A.type = t1; B.type = t2;
+  // coordinates relative to shape 1's centre (the CUDA kernel does the same: identical arithmetic on both sides)
+  for (int k = 0; k < 3; k++) { A.size[k] = s1[k]; A.pos[k] = 0; B.size[k] = s2[k]; B.pos[k] = p2[k] - p1[k]; }
+  for (int k = 0; k < 9; k++) { A.mat[k] = m1[k]; B.mat[k] = m2[k]; }
+  double depth, dir[3], pos[3];
+  if (!mjs_mpr_penetration<double>(A, B, &depth, dir, pos)) return 0;
+  c->dist = -depth;
+  set3(c->normal, dir);
+  for (int k = 0; k < 3; k++) c->pos[k] = pos[k] + p1[k];
+  c->yhint[0] = c->yhint[1] = c->yhint[2] = 0;
+  return 1;
 }
 
 // Sphere x cylinder (restates mjc_SphereCylinder's three cases: side, cap, rim).
@@ -742,7 +798,11 @@ void collision(const MjsModel* m, Data* d) {
     else if (t1 == MJS_GEOM_SPHERE && t2 == MJS_GEOM_CYLINDER) n = sphere_cylinder(p1, s1[0], p2, m2, s2, margin, rc);
     else if (t1 == MJS_GEOM_SPHERE && t2 == MJS_GEOM_BOX) n = sphere_box(p1, s1[0], p2, m2, s2, margin, rc);
     else if (t1 == MJS_GEOM_CAPSULE && t2 == MJS_GEOM_CAPSULE) n = capsule_capsule(p1, m1, s1, p2, m2, s2, margin, rc);
-    else if (t1 == MJS_GEOM_CYLINDER && t2 == MJS_GEOM_CYLINDER) n = cylinder_cylinder(p1, m1, s1, p2, m2, s2, margin, rc);
+    else if (t1 == MJS_GEOM_CYLINDER && t2 == MJS_GEOM_CYLINDER) {
+      n = cylinder_cylinder(p1, m1, s1, p2, m2, s2, margin, rc);
+      if (n < 0) n = convex_pair(t1, p1, m1, s1, t2, p2, m2, s2, rc);  // cap-cap / cap-rim / cap-side
+    }
+    else if ((t1 == MJS_GEOM_CAPSULE || t1 == MJS_GEOM_CYLINDER) && (t2 == MJS_GEOM_CYLINDER || t2 == MJS_GEOM_BOX)) n = convex_pair(t1, p1, m1, s1, t2, p2, m2, s2, rc);
     else { d->status |= MJS_STATUS_UNSUPPORTED_PAIR; continue; }
     d->flops += 60;
     if (n < 0) { d->status |= MJS_STATUS_UNSUPPORTED_PAIR; continue; }
@@ -1446,6 +1506,8 @@ void control_step(const MjsModel* m, const MjsTask* t, MjsEnvState* s, const dou
   }
   s->status |= d.status;
   write_obs_reward(m, t, s, &d, out);
+  // an unsupported geom pair or a contact overflow during this step cuts the episode (same rule as the CUDA step kernel)
+  if (d.status & (MJS_STATUS_UNSUPPORTED_PAIR | MJS_STATUS_CONTACT_OVERFLOW)) { out->done = 1; out->truncated = 1; out->terminated = 0; }
   if (flops) *flops += d.flops;
 }
 
@@ -1464,6 +1526,15 @@ extern "C" {
 // one control step for n envs (AoS states), OpenMP-free; callers thread by range
 void oracle_control_step(const MjsModel* m, const MjsTask* t, MjsEnvState* states, const double* actions, MjsStepOut* outs, int n, double tol_scale, long* flops) {
   for (int e = 0; e < n; e++) control_step(m, t, states + e, actions + (size_t)e * t->action_dim, outs + e, tol_scale, flops);
+}
+
+// MPR penetration of two primitives (include/mjs_convex.h) for the CPU tests: out = depth, dir[3], pos[3]; returns 1 on contact
+int oracle_convex_pair(int t1, const double* size1, const double* pos1, const double* mat1, int t2, const double* size2, const double* pos2, const double* mat2, double* out) {
+  MjsShape<double> A, B;
+  A.type = t1; B.type = t2;
+  for (int k = 0; k < 3; k++) { A.size[k] = size1[k]; A.pos[k] = pos1[k]; B.size[k] = size2[k]; B.pos[k] = pos2[k]; }
+  for (int k = 0; k < 9; k++) { A.mat[k] = mat1[k]; B.mat[k] = mat2[k]; }
+  return mjs_mpr_penetration<double>(A, B, out, out + 1, out + 4);
 }
 
 // world poses of every model geom at the given state (mj_kinematics): xpos[ngeom][3], xmat[ngeom][9].  Feeds the numpy

@@ -21,7 +21,8 @@ _LIB = _DIR / "_build" / "libmjs_oracle.so"
 def build(force: bool = False):
     src = _DIR / "mjs_oracle.cpp"
     hdr = _DIR.parent / "include" / "mjs_model.h"
-    if force or not _LIB.exists() or _LIB.stat().st_mtime < max(src.stat().st_mtime, hdr.stat().st_mtime):
+    hdr2 = _DIR.parent / "include" / "mjs_convex.h"
+    if force or not _LIB.exists() or _LIB.stat().st_mtime < max(src.stat().st_mtime, hdr.stat().st_mtime, hdr2.stat().st_mtime):
         subprocess.check_call(["make", "-C", str(_DIR), "-s", "-B"])
     return _LIB
 
@@ -173,3 +174,11 @@ def ur_ik_closest(dh, T, seed):
     q = np.zeros(6)
     ok = lib().oracle_ur_ik_closest(_dp(np.asarray(dh, float)), _dp(np.ascontiguousarray(T, float).ravel()), _dp(np.asarray(seed, float)), _dp(q))
     return q if ok else None
+
+
+def convex_pair(t1, size1, pos1, mat1, t2, size2, pos2, mat2):
+    """MPR penetration of two primitives (include/mjs_convex.h): None or (depth, dir[3], pos[3])"""
+    out = np.zeros(7)
+    f = lambda a, n: _dp(np.ascontiguousarray(np.asarray(a, float).ravel()[:n] if np.size(a) >= n else np.concatenate([np.ravel(a), np.zeros(n - np.size(a))])))
+    ok = lib().oracle_convex_pair(int(t1), f(size1, 3), f(pos1, 3), f(mat1, 9), int(t2), f(size2, 3), f(pos2, 3), f(mat2, 9), _dp(out))
+    return (out[0], out[1:4].copy(), out[4:7].copy()) if ok else None

@@ -61,5 +61,5 @@ def test_render_argument_checks_and_custom_resolution():
     img = env.render(width=48, height=32)
     assert img.shape == (3, 32, 48, 3)
     with pytest.raises(lib.MjsimError, match="bad image size"):
-        env.render(width=-1, height=8)
+        env.render(width=5000, height=8)
     env.close()
