@@ -251,8 +251,17 @@ __device__ __forceinline__ bool cyl_separated(const real* dif, const real* a1, r
 
 // separating axis of this lane's pair found by the last miss of the general convex routine (zero: none); lives in the pair
 // lane's registers for the rest of the control step
+#ifdef MJS_NO_SEPCACHE   // A/B build: no cache (nothing carried through the substep)
+template <typename real>
+struct SepAxis { static constexpr float v[3] = {0.f, 0.f, 0.f}; };
+#define MJS_SEP_SET(S, H, N) do { } while (0)
+#define MJS_SEP_ZERO {}
+#else
 template <typename real>
 struct SepAxis { float v[3]; };  // FP32 on purpose: any axis gives a sound test, and it lives in registers across the whole substep
+#define MJS_SEP_SET(S, H, N) do { (S).v[0] = (H) ? 0.f : (float)(N)[0]; (S).v[1] = (H) ? 0.f : (float)(N)[1]; (S).v[2] = (H) ? 0.f : (float)(N)[2]; } while (0)
+#define MJS_SEP_ZERO {{0, 0, 0}}
+#endif
 template <typename real>
 __device__ __forceinline__ bool cyl_axis_separates(const real* dif, const real* a1, real r1, real h1, const real* a2, real r2, real h2, const real* d) {
   real n2 = dot3(d, d);
@@ -1606,7 +1615,7 @@ struct ArmEngine {
       atomicAdd(&W.ncvx, 1);
 #endif
       const ConvexHit<real> ch = convex_pair_dev<real>(g1, g2, W.gpos[g1], W.gmat[g1], W.gpos[g2], W.gmat[g2]);
-      sep.v[0] = ch.hit ? 0.f : (float)ch.n[0]; sep.v[1] = ch.hit ? 0.f : (float)ch.n[1]; sep.v[2] = ch.hit ? 0.f : (float)ch.n[2];
+      MJS_SEP_SET(sep, ch.hit, ch.n);
       if (ch.hit && ch.dist < GM().pair_incl[lane]) {  // mj_collision: contacts with dist >= margin - gap produce no rows
 #ifdef MJS_CONVEX_COUNT
         atomicAdd(&W.ncvx_hit, 1);
@@ -1636,10 +1645,46 @@ struct ArmEngine {
   // composer loop's "step2 then step1" order is the same sequence seen from the
   // state's point of view (ArmTask::control_step).  Deliberately NOT inlined:
   // one copy of the heavy code keeps the instruction footprint inside the i-cache.
-  __device__ static __noinline__ SubRes substep(WM* Wp, int lane, real a_i, double time, int do_integrate, SepAxis<real> sep = SepAxis<real>{{0, 0, 0}}) {
+#ifdef MJS_SUBSTEP_ONE_PIECE
+  __device__ static __noinline__ SubRes substep(WM* Wp, int lane, real a_i, double time, int do_integrate, SepAxis<real> sep = SepAxis<real>MJS_SEP_ZERO) {
     const AM& A = cmodel<real>();
     WM& W = *Wp;
     ConReg C;
+    if (!(do_integrate & 2)) stage_sync(W, 1);
+    long long tclk = clock64(); (void)tclk;
+    kinematics(A, W, lane);
+    STAGE_CLK(W, 0, tclk);
+    stage_sync(W, 3);
+    bool clamped = dynamics(A, W, lane);
+    STAGE_CLK(W, 1, tclk);
+    stage_sync(W, 3);
+    bool cvx;
+    collide(A, W, lane, sep, cvx);
+    if (__any_sync(FULLMASK, cvx)) sep = convex_fixup(&W, lane, cvx, sep);  // rare: pairs without an analytic routine (cap contacts)
+    STAGE_CLK(W, 2, tclk);
+    stage_sync(W, 3);
+    make_rows(A, W, lane, C);
+    STAGE_CLK(W, 3, tclk);
+    stage_sync(W, 2);
+    SubRes r;
+    r.niter = solve(A, W, lane, C, a_i);
+    tclk = clock64();
+    r.touch = touch_force(A, W, lane, C);
+    stage_sync(W, 3);
+    if (do_integrate & 1) integrate(A, W, lane, clamped, time);
+    STAGE_CLK(W, 9, tclk);
+    r.a_i = a_i;
+    r.time = time;
+    r.sep = sep;
+    return r;
+  }
+#else
+  // The substep is two non-inlined halves -- mj_step1 up to the narrowphase, then rows / solve / integrate -- with the rare
+  // general-convex post-pass called between them from this small inlined wrapper: a call from inside either half costs the
+  // half its registers (profiles/r2/convex_pairs.txt).
+  __device__ static __noinline__ int substep_front(WM* Wp, int lane, int do_integrate, SepAxis<real> sep) {
+    const AM& A = cmodel<real>();
+    WM& W = *Wp;
     if (!(do_integrate & 2)) stage_sync(W, 1);
     long long tclk = clock64(); (void)tclk;
 #ifdef MJS_STAGE_CLOCKS_REPEAT  // experiment: the same (non-inlined) stage twice; the second run is hot in the instruction cache
@@ -1661,15 +1706,22 @@ struct ArmEngine {
     STAGE_CLK(W, 2, tclk);
     collide_only(&W, lane);
     STAGE_CLK(W, 13, tclk);
+    bool cvx = false;
 #else
     bool clamped = dynamics(A, W, lane);
     STAGE_CLK(W, 1, tclk);
     stage_sync(W, 3);
     bool cvx;
     collide(A, W, lane, sep, cvx);
-    if (__any_sync(FULLMASK, cvx)) sep = convex_fixup(&W, lane, cvx, sep);  // rare: pairs without an analytic routine (cap contacts)
     STAGE_CLK(W, 2, tclk);
 #endif
+    return (clamped ? 1 : 0) | (cvx ? 2 : 0);
+  }
+  __device__ static __noinline__ SubRes substep_back(WM* Wp, int lane, real a_i, double time, int do_integrate, bool clamped) {
+    const AM& A = cmodel<real>();
+    WM& W = *Wp;
+    ConReg C;
+    long long tclk = clock64(); (void)tclk;
     stage_sync(W, 3);
     make_rows(A, W, lane, C);
     STAGE_CLK(W, 3, tclk);
@@ -1683,12 +1735,19 @@ struct ArmEngine {
     STAGE_CLK(W, 9, tclk);
     r.a_i = a_i;
     r.time = time;
+    return r;
+  }
+  __device__ static __forceinline__ SubRes substep(WM* Wp, int lane, real a_i, double time, int do_integrate, SepAxis<real> sep = SepAxis<real>MJS_SEP_ZERO) {
+    const int f = substep_front(Wp, lane, do_integrate, sep);
+    if (__any_sync(FULLMASK, (f & 2) != 0)) sep = convex_fixup(Wp, lane, (f & 2) != 0, sep);  // rare: pairs without an analytic routine (cap contacts)
+    SubRes r = substep_back(Wp, lane, a_i, time, do_integrate, (f & 1) != 0);
     r.sep = sep;
     return r;
   }
+#endif
   __device__ static __noinline__ void kinematics_only(WM* Wp, int lane) { kinematics(cmodel<real>(), *Wp, lane); }
   __device__ static __noinline__ bool dynamics_only(WM* Wp, int lane) { return dynamics(cmodel<real>(), *Wp, lane); }
-  __device__ static __noinline__ void collide_only(WM* Wp, int lane) { SepAxis<real> sep = {{0, 0, 0}}; bool cvx; collide(cmodel<real>(), *Wp, lane, sep, cvx); }
+  __device__ static __noinline__ void collide_only(WM* Wp, int lane) { SepAxis<real> sep = MJS_SEP_ZERO; bool cvx; collide(cmodel<real>(), *Wp, lane, sep, cvx); }
 };
 
 // ===================================================================== analytic UR IK
@@ -2005,7 +2064,7 @@ struct ArmTask {
     }
     int nit_sum = 0, nit_max = 0;
     o.h4 = o.h8 = o.h16 = o.h32 = 0;
-    SepAxis<real> sep = {{0, 0, 0}};  // per pair lane: separating axis cached across the substeps of this control step
+    SepAxis<real> sep = MJS_SEP_ZERO;  // per pair lane: separating axis cached across the substeps of this control step
     for (int k = 0; k < A.n_sub; k++) {
       before_substep(A, W, lane, T);
       typename E::SubRes so = E::substep(&W, lane, a_i, T.time, (k % W.period) ? 3 : 1, sep);  // bit 1: skip the substep-start barrier
