@@ -130,7 +130,10 @@ int arm_step(ArmSim* a, const float* d_actions, float* d_obs, float* d_reward, u
   }
   // Work distribution of the step kernel: MJS_QUEUE=1 -> persistent grid, warps pull envs from an atomic counter
   // (no lock-step: sync_level 0); MJS_QUEUE=0 -> one block per 12/16 envs with lock-step stage barriers.
-  static const int use_queue = getenv("MJS_QUEUE") ? atoi(getenv("MJS_QUEUE")) : MJS_QUEUE_DEFAULT;
+  // Default per precision (profiles/r2/sync_queue_sweep.txt): f64 -> queue (2.32 M vs 2.20 M env-steps/s), FP32 -> lock-step blocks
+  // of 16 warps (2.94 M vs 1.60 M: the FP32 kernel's 16 free-running warps do not share instruction fetches).
+  static const int queue_env = getenv("MJS_QUEUE") ? atoi(getenv("MJS_QUEUE")) : -1;
+  const int use_queue = queue_env >= 0 ? queue_env : (a->precision == 0 ? MJS_QUEUE_DEFAULT : 0);
   if (use_queue) {
     io.sync_level = 0;
     io.queue = a->queue;

@@ -427,11 +427,47 @@ struct ArmEngine {
     __syncwarp();
   }
 
+  // spatial inertia about the world origin and inertial + gravity force of inertial body `a` riding on link `mylink`
+  __device__ static __forceinline__ void body_inertia_force(const AM& A, const WM& W, int a, int mylink, const real* vb, const real* ab, real* I, real* f) {
+    const real* R = W.xmat[SLOT_LINK0 + mylink];
+    real cl[3] = {GM().ab_com[a][0], GM().ab_com[a][1], GM().ab_com[a][2]}, h[3];
+    mat_vec(h, R, cl);
+    h[0] += W.xpos[SLOT_LINK0 + mylink][0]; h[1] += W.xpos[SLOT_LINK0 + mylink][1]; h[2] += W.xpos[SLOT_LINK0 + mylink][2];
+    // Ic_world = R * Ilocal * R^T
+    real Il[9] = {GM().ab_I[a][0], GM().ab_I[a][3], GM().ab_I[a][4], GM().ab_I[a][3], GM().ab_I[a][1], GM().ab_I[a][5], GM().ab_I[a][4], GM().ab_I[a][5], GM().ab_I[a][2]};
+    real T[9];
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+      for (int c = 0; c < 3; c++) T[3 * r + c] = R[3 * r] * Il[c] + R[3 * r + 1] * Il[3 + c] + R[3 * r + 2] * Il[6 + c];
+    real Ic[6];  // xx yy zz xy xz yz
+    Ic[0] = T[0] * R[0] + T[1] * R[1] + T[2] * R[2];
+    Ic[1] = T[3] * R[3] + T[4] * R[4] + T[5] * R[5];
+    Ic[2] = T[6] * R[6] + T[7] * R[7] + T[8] * R[8];
+    Ic[3] = T[0] * R[3] + T[1] * R[4] + T[2] * R[5];
+    Ic[4] = T[0] * R[6] + T[1] * R[7] + T[2] * R[8];
+    Ic[5] = T[3] * R[6] + T[4] * R[7] + T[5] * R[8];
+    real mass = GM().ab_mass[a], hh = dot3(h, h);
+    I[0] = mass; I[1] = mass * h[0]; I[2] = mass * h[1]; I[3] = mass * h[2];
+    I[4] = Ic[0] + mass * (hh - h[0] * h[0]); I[5] = Ic[1] + mass * (hh - h[1] * h[1]); I[6] = Ic[2] + mass * (hh - h[2] * h[2]);
+    I[7] = Ic[3] - mass * h[0] * h[1]; I[8] = Ic[4] - mass * h[0] * h[2]; I[9] = Ic[5] - mass * h[1] * h[2];
+    real fa[6], iv[6], g[6];
+    spi_mul(fa, I, ab);
+    spi_mul(iv, I, vb);
+    cross_force(g, vb, iv);
+    // net gravity (after compensation) as a spatial force at the com
+    real Fg[3] = {GM().ab_gfac[a] * mass * A.gravity[0], GM().ab_gfac[a] * mass * A.gravity[1], GM().ab_gfac[a] * mass * A.gravity[2]}, tg[3];
+    cross3(tg, h, Fg);
+#pragma unroll
+    for (int k = 0; k < 3; k++) { f[k] = fa[k] + g[k] - tg[k]; f[3 + k] = fa[3 + k] + g[3 + k] - Fg[k]; }
+  }
+
   // -------------------------------------------- [P2,P6,P7] CRB, RNE bias, actuation
   // Leaves Marm (joint-space inertia of the chain) and fsm = qfrc_smooth =
   // qfrc_passive - qfrc_bias + qfrc_actuator for every dof.  Gravity compensation
   // (robot.py:81-82) is folded into the RNE gravity term: each body feels
   // (1 - gravcomp) * m * g.  Returns the actuator "force is clamped" flag (lane j).
+#ifdef MJS_DYNAMICS_SCAN
   __device__ static bool dynamics(const AM& A, WM& W, int lane) {
     real Sj[6] = {0, 0, 0, 0, 0, 0}, qd = 0;
     if (lane < ARM_NLINK) {
@@ -471,39 +507,7 @@ struct ArmEngine {
     real vb[6], ab[6];
 #pragma unroll
     for (int k = 0; k < 6; k++) { vb[k] = shfl(v[k], mylink); ab[k] = shfl(acc[k], mylink); }
-    if (lane < A.nab) {
-      const real* R = W.xmat[SLOT_LINK0 + mylink];
-      real cl[3] = {GM().ab_com[lane][0], GM().ab_com[lane][1], GM().ab_com[lane][2]}, h[3];
-      mat_vec(h, R, cl);
-      h[0] += W.xpos[SLOT_LINK0 + mylink][0]; h[1] += W.xpos[SLOT_LINK0 + mylink][1]; h[2] += W.xpos[SLOT_LINK0 + mylink][2];
-      // Ic_world = R * Ilocal * R^T
-      real Il[9] = {GM().ab_I[lane][0], GM().ab_I[lane][3], GM().ab_I[lane][4], GM().ab_I[lane][3], GM().ab_I[lane][1], GM().ab_I[lane][5], GM().ab_I[lane][4], GM().ab_I[lane][5], GM().ab_I[lane][2]};
-      real T[9];
-#pragma unroll
-      for (int r = 0; r < 3; r++)
-#pragma unroll
-        for (int c = 0; c < 3; c++) T[3 * r + c] = R[3 * r] * Il[c] + R[3 * r + 1] * Il[3 + c] + R[3 * r + 2] * Il[6 + c];
-      real Ic[6];  // xx yy zz xy xz yz
-      Ic[0] = T[0] * R[0] + T[1] * R[1] + T[2] * R[2];
-      Ic[1] = T[3] * R[3] + T[4] * R[4] + T[5] * R[5];
-      Ic[2] = T[6] * R[6] + T[7] * R[7] + T[8] * R[8];
-      Ic[3] = T[0] * R[3] + T[1] * R[4] + T[2] * R[5];
-      Ic[4] = T[0] * R[6] + T[1] * R[7] + T[2] * R[8];
-      Ic[5] = T[3] * R[6] + T[4] * R[7] + T[5] * R[8];
-      real mass = GM().ab_mass[lane], hh = dot3(h, h);
-      I[0] = mass; I[1] = mass * h[0]; I[2] = mass * h[1]; I[3] = mass * h[2];
-      I[4] = Ic[0] + mass * (hh - h[0] * h[0]); I[5] = Ic[1] + mass * (hh - h[1] * h[1]); I[6] = Ic[2] + mass * (hh - h[2] * h[2]);
-      I[7] = Ic[3] - mass * h[0] * h[1]; I[8] = Ic[4] - mass * h[0] * h[2]; I[9] = Ic[5] - mass * h[1] * h[2];
-      real fa[6], iv[6], g[6];
-      spi_mul(fa, I, ab);
-      spi_mul(iv, I, vb);
-      cross_force(g, vb, iv);
-      // net gravity (after compensation) as a spatial force at the com
-      real Fg[3] = {GM().ab_gfac[lane] * mass * A.gravity[0], GM().ab_gfac[lane] * mass * A.gravity[1], GM().ab_gfac[lane] * mass * A.gravity[2]}, tg[3];
-      cross3(tg, h, Fg);
-#pragma unroll
-      for (int k = 0; k < 3; k++) { f[k] = fa[k] + g[k] - tg[k]; f[3 + k] = fa[3 + k] + g[3 + k] - Fg[k]; }
-    }
+    if (lane < A.nab) body_inertia_force(A, W, lane, mylink, vb, ab, I, f);
     // fold the fixed attachments (lanes 6,7) into their link lane
 #pragma unroll ROLL
     for (int a = ARM_NLINK; a < ARM_MAXAB; a++) {
@@ -528,6 +532,54 @@ struct ArmEngine {
 #pragma unroll
       for (int k = 0; k < 6; k++) { real t = shfl_down(f[k], o); if (lane + o < ARM_NLINK) f[k] += t; }
     }
+#else
+  // Every inertial-body lane (6 links + <= 2 fixed attachments) walks the chain up to its own link in registers -- motion axes and
+  // joint rates come from shared memory -- instead of prefix scans through shuffles; the bodies' spatial inertias and forces go
+  // through a shared-memory scratch (the contact Jacobian block, free until make_rows) and every link lane sums its sub-chain.
+  // No shuffle in the stage: 10.2 k -> see profiles/r2/stage_cycles.txt.
+  __device__ static bool dynamics(const AM& A, WM& W, int lane) {
+    real Sj[6] = {0, 0, 0, 0, 0, 0};
+    const int mylink = lane < A.nab ? GM().ab_link[lane] : -1;
+    real vb[6] = {0, 0, 0, 0, 0, 0}, ab[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll 1
+    for (int j = 0; j <= mylink; j++) {
+      real s[6], sd[6];
+      const real qd = (real)W.qvel[j];
+#pragma unroll
+      for (int k = 0; k < 6; k++) s[k] = W.S[j][k];
+      cross_motion(sd, vb, s);  // uses the velocity of the parent link
+#pragma unroll
+      for (int k = 0; k < 6; k++) { ab[k] += sd[k] * qd; vb[k] += s[k] * qd; }
+    }
+    if (lane < ARM_NLINK) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) Sj[k] = W.S[lane][k];
+    }
+    real I[10], f[6];
+    if (lane < A.nab) {
+      body_inertia_force(A, W, lane, mylink, vb, ab, I, f);
+#pragma unroll
+      for (int k = 0; k < 10; k++) W.cJ[lane][k] = I[k];
+#pragma unroll
+      for (int k = 0; k < 6; k++) W.cJ[lane][10 + k] = f[k];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 10; k++) I[k] = 0;
+#pragma unroll
+    for (int k = 0; k < 6; k++) f[k] = 0;
+    if (lane < ARM_NLINK) {
+#pragma unroll 1
+      for (int a = 0; a < A.nab; a++) {
+        if (GM().ab_link[a] >= lane) {
+#pragma unroll
+          for (int k = 0; k < 10; k++) I[k] += W.cJ[a][k];
+#pragma unroll
+          for (int k = 0; k < 6; k++) f[k] += W.cJ[a][10 + k];
+        }
+      }
+    }
+#endif
     bool clamped = false;
     if (lane < ARM_NLINK) {
       real tau = 0;

@@ -14,7 +14,7 @@
 #define ARM_STEP_WPB_F64 12  // 12 x 19.3 KB of FP64 WarpMem fill the 227 KB of one SM; 168 regs x 384 threads fit the RF
 #endif
 #ifndef MJS_QUEUE_DEFAULT
-#define MJS_QUEUE_DEFAULT 0
+#define MJS_QUEUE_DEFAULT 1  // persistent grid + atomic work queue: measured faster than the lock-step blocks since the round-2 code shrink (profiles/r2/sync_queue_sweep.txt)
 #endif
 #ifndef ARM_STEP_SYNC
 #define ARM_STEP_SYNC true

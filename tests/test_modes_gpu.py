@@ -40,3 +40,5 @@ def test_lock_step_levels_and_work_queue_do_not_change_results(prec):
     for level in (0, 3, 49):
         assert _digest(prec, MJS_SYNC_LEVEL=level) == ref, f"MJS_SYNC_LEVEL={level}"
     assert _digest(prec, MJS_QUEUE=1) == ref, "MJS_QUEUE=1"
+    for level in (0, 1, 3):  # the static grid (one block per 12 / 16 envs) with its lock-step levels
+        assert _digest(prec, MJS_QUEUE=0, MJS_SYNC_LEVEL=level) == ref, f"MJS_QUEUE=0 MJS_SYNC_LEVEL={level}"
