@@ -1883,25 +1883,33 @@ struct ArmEngine {
 // Device restatement of oracle/mjs_oracle.cpp ur_ik_all / ur_ik_closest (which
 // restates ur_analytic_ik.ur5e.inverse_kinematics_closest, robot.py:31-38).
 // Lane s (0..7) evaluates branch (s1, s5, s3) = bits (4, 2, 1); double precision.
-__device__ inline void dh_T(double* T, double th, double dd, double a, double al) {
-  double st, ct, sa, ca;
-  sincos(th, &st, &ct);
-  sincos(al, &sa, &ca);
+// DH transform with the link twist given by its sine / cosine (the twists of the UR chain are 0 and +-pi/2: constants at every call
+// site, where the library sincos(alpha) cost ~160 instructions each time); the joint angle uses the kernel's short sincos.
+__device__ __forceinline__ void dh_T(double* T, double th, double dd, double a, double sa, double ca) {
+  double st, ct;
+  sincos_r<double>(th, &st, &ct);
   T[0] = ct; T[1] = -st * ca; T[2] = st * sa; T[3] = a * ct;
   T[4] = st; T[5] = ct * ca; T[6] = -ct * sa; T[7] = a * st;
   T[8] = 0; T[9] = sa; T[10] = ca; T[11] = dd;
 }
-__device__ inline void mul34(double* C, const double* A, const double* B) {  // rigid 3x4 products
+// (loops fully unrolled: the 3x4 arrays must be indexed statically to stay in registers -- the once-per-step code was the
+// kernel's only local-memory traffic, 3.2 kB per env-step of DRAM writes in round 1)
+__device__ __forceinline__ void mul34(double* C, const double* A, const double* B) {  // rigid 3x4 products
   double R[12];
+#pragma unroll
   for (int i = 0; i < 3; i++) {
+#pragma unroll
     for (int j = 0; j < 3; j++) R[4 * i + j] = A[4 * i] * B[j] + A[4 * i + 1] * B[4 + j] + A[4 * i + 2] * B[8 + j];
     R[4 * i + 3] = A[4 * i] * B[3] + A[4 * i + 1] * B[7] + A[4 * i + 2] * B[11] + A[4 * i + 3];
   }
+#pragma unroll
   for (int i = 0; i < 12; i++) C[i] = R[i];
 }
-__device__ inline void inv34(double* B, const double* A) {
+__device__ __forceinline__ void inv34(double* B, const double* A) {
   double R[12] = {A[0], A[4], A[8], 0, A[1], A[5], A[9], 0, A[2], A[6], A[10], 0};
+#pragma unroll
   for (int i = 0; i < 3; i++) R[4 * i + 3] = -(R[4 * i] * A[3] + R[4 * i + 1] * A[7] + R[4 * i + 2] * A[11]);
+#pragma unroll
   for (int i = 0; i < 12; i++) B[i] = R[i];
 }
 #define MJS_PI 3.14159265358979323846
@@ -1920,7 +1928,7 @@ __device__ inline bool ur_ik_closest_warp(const double* dh, const double* T06, c
     double psi = atan2(p05[1], p05[0]), phi = acos(d4 / rxy);
     double th1 = psi + (s1 == 0 ? phi : -phi) + MJS_PI / 2;
     double T01[12], T10[12], T16[12];
-    dh_T(T01, th1, d1, 0, MJS_PI / 2);
+    dh_T(T01, th1, d1, 0, 1.0, 0.0);
     inv34(T10, T01);
     mul34(T16, T10, T06);
     double c5 = T16[10];
@@ -1936,8 +1944,8 @@ __device__ inline bool ur_ik_closest_warp(const double* dh, const double* T06, c
         th234 = atan2(T16[6] / -sn5, T16[2] / -sn5);
       }
       double T45[12], T56[12], T46[12], T64[12], T14[12];
-      dh_T(T45, th5, d5, 0, -MJS_PI / 2);
-      dh_T(T56, th6, d6, 0, 0);
+      dh_T(T45, th5, d5, 0, -1.0, 0.0);
+      dh_T(T56, th6, d6, 0, 0.0, 1.0);
       mul34(T46, T45, T56);
       inv34(T64, T46);
       mul34(T14, T16, T64);
@@ -1950,11 +1958,13 @@ __device__ inline bool ur_ik_closest_warp(const double* dh, const double* T06, c
         double th4 = th234 - th2 - th3;
         q[0] = th1; q[1] = th2; q[2] = th3; q[3] = th4; q[4] = th5; q[5] = th6;
         dist = 0;
+#pragma unroll
         for (int i = 0; i < 6; i++) {
           double v = fmod(q[i] + MJS_PI, 2 * MJS_PI);
           if (v < 0) v += 2 * MJS_PI;
           v -= MJS_PI;
           double bq = v, bd = fabs(v - seed[i]);
+#pragma unroll
           for (int w = -1; w <= 1; w += 2) {
             double c = v + w * 2 * MJS_PI;
             if (c >= -2 * MJS_PI && c <= 2 * MJS_PI && fabs(c - seed[i]) < bd) { bd = fabs(c - seed[i]); bq = c; }
@@ -1975,6 +1985,7 @@ __device__ inline bool ur_ik_closest_warp(const double* dh, const double* T06, c
     int ol = __shfl_xor_sync(FULLMASK, bl, o);
     if (od < best || (od == best && ol < bl)) { best = od; bl = ol; }
   }
+#pragma unroll
   for (int i = 0; i < 6; i++) qout[i] = __shfl_sync(FULLMASK, q[i], bl);
   return best < 1e299;
 }
@@ -2180,6 +2191,31 @@ struct ArmTask {
     o.success = has_success ? (accomplished ? 1 : 0) : 0;
   }
 
+  struct SubLoop { real a_i; double time, t0, tq0, tq1; int traj, swa, swp, swc, nit_sum, nit_max; };
+  __device__ static __noinline__ SubLoop run_substeps(WM* Wp, int lane, SubLoop s) {
+    const AM& A = cmodel<real>();
+    WM& W = *Wp;
+    SepAxis<real> sep = MJS_SEP_ZERO;  // per pair lane: separating axis cached across the substeps of this control step
+    for (int k = 0; k < A.n_sub; k++) {
+      if (s.traj && lane < ARM_NLINK) {  // before_substep: joint_trajectory.py:33-47 + robot.py:261-272
+        double t0 = s.t0, t1 = s.t0 + A.control_dt;
+        double tt = fmin(fmax(s.time, t0), t1);
+        W.ctrl[lane] = s.tq0 + (s.tq1 - s.tq0) * (tt - t0) / (t1 - t0);
+      }
+      __syncwarp();
+      typename E::SubRes so = E::substep(&W, lane, s.a_i, s.time, (k % W.period) ? 3 : 1, sep);  // bit 1: skip the substep-start barrier
+      s.a_i = so.a_i; s.time = so.time; sep = so.sep;
+      s.nit_sum += so.niter; s.nit_max = so.niter > s.nit_max ? so.niter : s.nit_max;
+      if (A.kind == MJS_TASK_BUTTON) {  // switch.py:51-60, evaluated after every substep
+        int was = s.swp;
+        s.swp = ((double)so.touch >= A.touch_lo && (double)so.touch <= A.touch_hi) ? 1 : 0;
+        if (s.swp && !was) s.swa = !s.swa;
+        s.swc += s.swp;
+      }
+    }
+    return s;
+  }
+
   // One control step for the env owned by this warp (composer loop)
   __device__ static void control_step(const AM& A, WM& W, int lane, TS& T, real& a_i, const double* action, Out& o, const ArmIO& io, int e) {
     if (A.kind == MJS_TASK_REACH) servoL(A, W, lane, T, action);
@@ -2191,19 +2227,16 @@ struct ArmTask {
       if (A.action_dim == 7) servoJ(W, lane, T, action);
       else servoL(A, W, lane, T, action);
     }
-    int nit_sum = 0, nit_max = 0;
     o.h4 = o.h8 = o.h16 = o.h32 = 0;
-    SepAxis<real> sep = MJS_SEP_ZERO;  // per pair lane: separating axis cached across the substeps of this control step
-    for (int k = 0; k < A.n_sub; k++) {
-      before_substep(A, W, lane, T);
-      typename E::SubRes so = E::substep(&W, lane, a_i, T.time, (k % W.period) ? 3 : 1, sep);  // bit 1: skip the substep-start barrier
-      a_i = so.a_i; T.time = so.time; sep = so.sep;
-      nit_sum += so.niter; nit_max = so.niter > nit_max ? so.niter : nit_max;
-#ifdef MJS_NIT_HIST
-      o.h4 += so.niter >= 3; o.h8 += so.niter >= 6; o.h16 += so.niter >= 12; o.h32 += so.niter >= 30;
-#endif
-      if (A.kind == MJS_TASK_BUTTON) switch_update(A, T, so.touch);
-    }
+    // the n_sub substeps run inside ONE non-inlined call that carries only what the loop needs: the two calls per substep
+    // (substep_front / substep_back) then save and restore a dozen registers instead of this function's whole task state
+    // (264 local-memory instructions per substep before, on the dependent path)
+    SubLoop sl;
+    sl.a_i = a_i; sl.time = T.time; sl.t0 = T.t0; sl.tq0 = T.tq0; sl.tq1 = T.tq1; sl.traj = T.traj;
+    sl.swa = T.swa; sl.swp = T.swp; sl.swc = T.swc; sl.nit_sum = 0; sl.nit_max = 0;
+    sl = run_substeps(&W, lane, sl);
+    a_i = sl.a_i; T.time = sl.time; T.swa = sl.swa; T.swp = sl.swp; T.swc = sl.swc;
+    const int nit_sum = sl.nit_sum, nit_max = sl.nit_max;
     // after_step (robot_push_button.py:159-165): an active, unpressed switch is deactivated with probability disturb_prob;
     // the draw is keyed by (seed, global env, episode, control step of the episode) on the DISTURB stream
     if (A.kind == MJS_TASK_BUTTON && A.button_disturbances && T.swa && !T.swp) {
