@@ -1915,7 +1915,7 @@ __device__ __forceinline__ void inv34(double* B, const double* A) {
 #define MJS_PI 3.14159265358979323846
 
 // all 32 lanes call; returns true (warp-uniform) and q[6] (identical in all lanes) on success
-__device__ inline bool ur_ik_closest_warp(const double* dh, const double* T06, const double* seed, double* qout, int lane) {
+__device__ __forceinline__ bool ur_ik_closest_warp(const double* dh, const double* T06, const double* seed, double* qout, int lane) {
   double d1 = dh[0], a2 = dh[1], a3 = dh[2], d4 = dh[3], d5 = dh[4], d6 = dh[5];
   double q[6] = {0, 0, 0, 0, 0, 0};
   double dist = 1e300;
@@ -2096,18 +2096,25 @@ struct ArmTask {
   }
 
   // robot.py:218-259 servoL / servoJ.  tcp == nullptr: joint target in qt (lane j holds qt_j in all lanes' array)
-  __device__ static void servoJ(WM& W, int lane, TS& T, const double* qt) {
-    if (lane < ARM_NLINK) { T.tq0 = W.qpos[lane]; T.tq1 = qt[lane]; }
+  __device__ static __forceinline__ void servoJ(WM& W, int lane, TS& T, const double* qt) {
+    if (lane < ARM_NLINK) {
+      T.tq0 = W.qpos[lane];
+      double v = 0;
+#pragma unroll
+      for (int k = 0; k < ARM_NLINK; k++) if (k == lane) v = qt[k];  // static indexing keeps the caller's array in registers
+      T.tq1 = v;
+    }
     T.t0 = T.time;
     T.traj = 1;
   }
-  __device__ static bool tcp_to_joints(const AM& A, const double* tcp, const double* seed, double* q, int lane) {
+  __device__ static __forceinline__ bool tcp_to_joints(const AM& A, const double* tcp, const double* seed, double* q, int lane) {
     // top-down flange pose (TOP_DOWN_QUATERNION = 180 deg about x), robot.py:138-151
     double T06[12] = {1, 0, 0, tcp[0] - (double)A.tcp_offset[0], 0, -1, 0, tcp[1] + (double)A.tcp_offset[1], 0, 0, -1, tcp[2] + (double)A.tcp_offset[2]};
     return ur_ik_closest_warp(A.ik_dh, T06, seed, q, lane);
   }
-  __device__ static void servoL(const AM& A, WM& W, int lane, TS& T, const double* tcp) {
+  __device__ static __forceinline__ void servoL(const AM& A, WM& W, int lane, TS& T, const double* tcp) {
     double seed[6], q[6];
+#pragma unroll
     for (int i = 0; i < 6; i++) seed[i] = W.qpos[i];
     if (!tcp_to_joints(A, tcp, seed, q, lane)) { T.status |= MJS_STATUS_IK_FAIL; return; }
     servoJ(W, lane, T, q);
@@ -2147,16 +2154,20 @@ struct ArmTask {
     tcp_position(A, W, tcp);
     bool accomplished = false, has_success = false;
     double reward = 0;
+#pragma unroll
     for (int k = 0; k < 16; k++) o.obs[k] = 0;
     if (A.kind == MJS_TASK_REACH) {
+#pragma unroll
       for (int k = 0; k < 3; k++) { o.obs[k] = tcp[k]; o.obs[3 + k] = T.target[k]; }
       double dist = sqrt((tcp[0] - T.target[0]) * (tcp[0] - T.target[0]) + (tcp[1] - T.target[1]) * (tcp[1] - T.target[1]) + (tcp[2] - T.target[2]) * (tcp[2] - T.target[2]));
       reward = A.reward_type == 0 ? (dist < A.goal_threshold ? 1.0 : 0.0) : -dist;
     } else if (A.kind == MJS_TASK_PUSH) {
+#pragma unroll
       for (int k = 0; k < 3; k++) o.obs[k] = tcp[k];
       o.obs[3] = T.target[0]; o.obs[4] = T.target[1];
       double sum = 0, nearest = 1e300;
       int within = 0;
+#pragma unroll
       for (int b = 0; b < NOBJ; b++) {
         double x = W.qpos[ARM_NLINK + 7 * b], y = W.qpos[ARM_NLINK + 7 * b + 1];
         o.obs[5 + 2 * b] = x; o.obs[6 + 2 * b] = y;
@@ -2169,11 +2180,13 @@ struct ArmTask {
       else reward = (-sum / NOBJ - A.nearest_coef * nearest) * 0.1;
       accomplished = within == NOBJ;
     } else {  // BUTTON
+#pragma unroll
       for (int k = 0; k < 6; k++) o.obs[k] = W.qpos[k];
       const real* R = W.xmat[A.touch_slot];
       real tp[3] = {A.touch_pos[0], A.touch_pos[1], A.touch_pos[2]}, v[3];
       mat_vec(v, R, tp);
       double quirk = 0.5 * ((double)A.touch_size[0] / 1.01);  // switch.py:86-87
+#pragma unroll
       for (int k = 0; k < 3; k++) o.obs[6 + k] = (double)W.xpos[A.touch_slot][k] + (double)v[k] + quirk;
       o.obs[9] = T.swa;
       double dg = sqrt((tcp[0] - A.button_goal[0]) * (tcp[0] - A.button_goal[0]) + (tcp[1] - A.button_goal[1]) * (tcp[1] - A.button_goal[1]) + (tcp[2] - A.button_goal[2]) * (tcp[2] - A.button_goal[2]));
@@ -2480,9 +2493,11 @@ __device__ __noinline__ void arm_step_env(const ArmModel<real>& A, WarpMem<real,
   double action[8];
   int AD = A.action_dim;
   if (io.actions) {
+#pragma unroll
     for (int k = 0; k < 8; k++) action[k] = k < AD ? (double)io.actions[(size_t)e * AD + k] : 0.0;
   } else {
     unsigned genv = io.env_offset + e;
+#pragma unroll
     for (int k = 0; k < 8; k++) {
       action[k] = 0;
       if (k < AD) {
