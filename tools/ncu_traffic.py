@@ -26,7 +26,7 @@ def main():
         i = col[name]
         return float(vals[i].replace(",", "")) * UNIT.get(units[i], 1.0)
 
-    keep = Path(sys.argv[4]) if len(sys.argv) > 4 else None
+    keep = (ROOT / sys.argv[4]).resolve() if len(sys.argv) > 4 else None
     if keep:
         shutil.copy(raw, keep)
     out_path = ROOT / "profiles" / "r2" / "traffic.json"
