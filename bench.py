@@ -234,9 +234,18 @@ def run_gpu(args):
     lo = torch.tensor([env.bundle.task.action_lo[k] for k in range(A)], device=dev)
     hi = torch.tensor([env.bundle.task.action_hi[k] for k in range(A)], device=dev)
     g = torch.Generator(device=dev); g.manual_seed(args.seed + 17 * rank)
-    total = args.warmup + args.steps
-    ring = 16  # pre-generated action batches resident in HBM, reused cyclically
-    actions = (lo + (hi - lo) * torch.rand(ring, N, A, device=dev, generator=g)).float().contiguous()
+    # Action batches are NEVER replayed cyclically: a short cycle of pusher targets sweeps the same path over and over, clears
+    # it of props and settles into a cheaper regime than uniform random actions (profiles/r2/step_trace*.txt: 16.7 vs 18.9 ms per
+    # step with a 16-batch ring).  Untimed steps draw a new batch per step; timed regions read pre-generated distinct batches.
+    ring = min(max(args.steps, 40), 1024)  # distinct batches resident in HBM for the timed regions (period >= the region or >= 2 episodes)
+
+    def draw(n_envs):
+        return (lo + (hi - lo) * torch.rand(n_envs, A, device=dev, generator=g)).float()
+
+    def batches(n_envs):
+        return (lo + (hi - lo) * torch.rand(ring, n_envs, A, device=dev, generator=g)).float().contiguous()
+
+    actions = batches(N) if args.workload == "planar_push" else None
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = torch.cuda.current_stream(dev)
     host_actions = args.workload == "planar_push"
@@ -287,14 +296,12 @@ def run_gpu(args):
     # ---- burn-in (untimed, not part of W): one full episode length, so that every env has gone through its
     # staggered reset and the population of physical states is stationary (fresh scenes cost ~10 % more per step
     # than the steady-state mix; a region timed right after reset() would drift)
-    for i in range(burn_in):
-        env.step_flat(actions[i % ring])
-    # ---- device-resident arm ("value")
-    for i in range(args.warmup):
-        env.step_flat(actions[i % ring])
+    for i in range(burn_in + args.warmup):  # burn-in, then the W warm-up steps of the device-resident arm ("value")
+        env.step_flat(draw(N) if host_actions else None)
+    torch.cuda.synchronize(dev)  # the clock sampler below should see the timed region, not the tail of the burn-in
     l0 = env.launch_count
     with ClockSampler(local) as clk:
-        t_ms = timed_region(lambda i: env.step_flat(actions[(args.warmup + i) % ring]), args.steps, env)
+        t_ms = timed_region(lambda i: env.step_flat(actions[i % ring]), args.steps, env)
     launches = env.launch_count - l0
     n_stats = n_allreduce[0]
     # flush cost alone, for the record
@@ -311,8 +318,9 @@ def run_gpu(args):
     env.join_aux(); torch.cuda.synchronize(dev)
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(kn + 1)]
     evs[0].record(stream)
+    k_actions = batches(N)[:kn] if host_actions else actions
     for i in range(kn):
-        env.step_flat(actions[i % ring])
+        env.step_flat(k_actions[i])
         evs[i + 1].record(stream)
     torch.cuda.synchronize(dev)
     per = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(kn))
@@ -321,7 +329,7 @@ def run_gpu(args):
     # ---- end-to-end arm: HOST buffers through the C-ABI host call (H2D + step + D2H + sync inside)
     h_act = torch.empty(ring, N, A, dtype=torch.float32).pin_memory()
     if host_actions:
-        h_act.copy_(actions.cpu())
+        h_act.copy_(batches(N).cpu())
     h_obs = torch.empty(N, O, dtype=torch.float32).pin_memory()
     h_rew = torch.empty(N, dtype=torch.float32).pin_memory()
     h_flg = torch.empty(N, 4, dtype=torch.uint8).pin_memory()
@@ -331,7 +339,7 @@ def run_gpu(args):
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
-        env.step_host(a_np[i % ring] if host_actions else None, o_np, r_np, f_np)
+        env.step_host(a_np[(i + 3) % ring] if host_actions else None, o_np, r_np, f_np)
     e2e_s = time.perf_counter() - t0
     e2e_t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
     if world > 1:
@@ -347,11 +355,11 @@ def run_gpu(args):
         env2.reset()
         if task == "robot_planar_push":
             _stagger_episodes(env2, env2.bundle.task.max_steps, args.seed + rank)
-        act2 = actions[:, :N2].contiguous() if N2 <= N else (lo + (hi - lo) * torch.rand(ring, N2, A, device=dev, generator=g)).float()
+        act2 = batches(N2)
         for i in range(burn_in + args.warmup):
-            env2.step_flat(act2[i % ring])
+            env2.step_flat(draw(N2))
         main_env, env = env, env2
-        t2 = timed_region(lambda i: env2.step_flat(act2[(args.warmup + i) % ring]), args.steps)
+        t2 = timed_region(lambda i: env2.step_flat(act2[i % ring]), args.steps)
         env = main_env
         env2.close()
         alt = {"precision": "mixed", "envs_per_gpu": N2, "value": world * N2 * args.steps / (t2 * 1e-3), "unit": "env-steps/s", "ms_per_step": t2 / args.steps,
@@ -363,11 +371,11 @@ def run_gpu(args):
         env3 = ms.make(task, SMALL_ENVS, device=dev, seed=args.seed, env_offset=sharding.env_offset(rank, SMALL_ENVS), precision=args.precision)
         env3.reset()
         _stagger_episodes(env3, env3.bundle.task.max_steps, args.seed + rank)
-        act3 = actions[:, :SMALL_ENVS].contiguous()
+        act3 = batches(SMALL_ENVS)
         for i in range(burn_in + args.warmup):
-            env3.step_flat(act3[i % ring])
+            env3.step_flat(draw(SMALL_ENVS))
         main_env, env = env, env3
-        t3 = timed_region(lambda i: env3.step_flat(act3[(args.warmup + i) % ring]), args.steps)
+        t3 = timed_region(lambda i: env3.step_flat(act3[i % ring]), args.steps)
         env = main_env
         env3.close()
         v3 = world * SMALL_ENVS * args.steps / (t3 * 1e-3)
@@ -395,7 +403,8 @@ def run_gpu(args):
             "config": {"workload": (f"{args.workload}: UR5e + cylinder pusher + 3 cylinder props, {env.bundle.task.n_sub} substeps/step, {N} envs/GPU" if host_actions
                                     else f"{args.workload}: {env.bundle.task.n_sub} substeps/step, {N} envs/GPU, device-drawn actions"),
                        "envs_per_gpu": N, "precision": args.precision, "l2": f"flushed between timed iterations (256 MiB memset inside the region, {flush_ms:.3f} ms each)",
-                       "episodes": f"phases staggered over [0,max_steps) + {burn_in} untimed burn-in steps: stationary state mix and auto-reset rate"},
+                       "episodes": f"phases staggered over [0,max_steps) + {burn_in} untimed burn-in steps: stationary state mix and auto-reset rate",
+                       "actions": "a new uniform random batch every control step, burn-in included (no cyclic replay)" if host_actions else "drawn on the device per step (Philox)"},
             "e2e": {"value": world * N * args.steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": N * A * 4 if host_actions else 0,
                     "d2h_bytes_per_step": N * (O + 1) * 4 + N * 4},
             "gpu_launches": int(launches),
