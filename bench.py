@@ -33,7 +33,7 @@ WORKLOADS = {
 METRIC = "env-steps/s (device-timed) Planar Push"
 SMALL_ENVS = 4096   # BASELINE.json configs[3] names "4096 envs per GPU": reported beside the headline as config_4096
 STATS_EVERY = 10    # control steps between two NCCL all-reduces of the statistics vector inside the timed region
-KERNEL_SOURCES = ["arm_kernel.cuh", "arm_model.cuh", "arm_launch.cuh", "arm_sim.cuh", "mjs_common.cuh", "arm.cu"]
+KERNEL_SOURCES = ["arm_kernel.cuh", "arm_model.cuh", "arm_launch.cuh", "arm_sim.cuh", "mjs_common.cuh", "arm.cu", "../../include/mjs_convex.h", "../../include/mjs_model.h"]
 MIXED_ENVS = 37888  # 148 SMs x 16 FP32 warps x 16 waves
 FP32_PEAK_TFLOPS_FALLBACK = 148 * 128 * 2 * 1.965e9 / 1e12  # SMs x FP32 lanes x FMA x clocks.max.sm = 74.4
 

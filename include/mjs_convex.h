@@ -263,17 +263,4 @@ MJS_HD inline int mjs_mpr_penetration(const MjsShape<T>& A, const MjsShape<T>& B
   }
 }
 
-/* Penetration of the two shapes along a given unit direction n (from shape 1 to shape 2): the overlap of their extents,
- * h1(n) + h2(-n) - (c2 - c1).n, evaluated with two support points.  Used to re-evaluate the depth of an MPR result in full
- * precision when the portal search itself ran in FP32 (CUDA kernel), and by the oracle, so both sides report the same
- * quantity: to first order it does not depend on the small difference between the two searches' directions.
- * The contact position stays the search's. */
-template <typename T>
-MJS_HD inline T mjs_directional_depth(const MjsShape<T>& A, const MjsShape<T>& B, const T* n) {
-  T a[3], b[3], nn[3] = {-n[0], -n[1], -n[2]};
-  mjsccd::shape_support(A, n, a);
-  mjsccd::shape_support(B, nn, b);
-  return (a[0] - b[0]) * n[0] + (a[1] - b[1]) * n[1] + (a[2] - b[2]) * n[2];
-}
-
 #endif /* MJS_CONVEX_H_ */

@@ -645,7 +645,6 @@ int cylinder_cylinder(const double* p1, const double* m1, const double* s1, cons
     (void)gap; (void)radial;
     // only a cap configuration can touch: the caller asks the general convex routine unless an axis separates the cylinders
     { bool sp = cyl_separated(dif, a1, s1[0], s1[1], a2, s2[0], s2[1], dif);
-      if (getenv("ORACLE_CVX_LOG") && !sp) fprintf(stderr, "CVX A h1 %.3f h2 %.3f cos %.3f tc %.4f dist %.4f z1 %.3f z2 %.3f\n", s1[1], s2[1], dot3(a1, a2), tc, norm3(dif), p1[2], p2[2]);
       return sp ? 0 : -1; }
   }
   double sm = 0.5 * (lo + hi);
@@ -664,7 +663,6 @@ int cylinder_cylinder(const double* p1, const double* m1, const double* s1, cons
   double axial_pen = std::min(s1[1], tc + ext) - std::max(-s1[1], tc - ext);
   if (radial_pen > 0 && axial_pen < radial_pen) {
     bool sp = cyl_separated(dif, a1, s1[0], s1[1], a2, s2[0], s2[1], dq);
-    if (getenv("ORACLE_CVX_LOG") && !sp) fprintf(stderr, "CVX B h1 %.3f h2 %.3f cos %.3f tc %.4f dist %.4f z1 %.3f z2 %.3f axpen %.4f radpen %.4f\n", s1[1], s2[1], dot3(a1, a2), tc, norm3(dif), p1[2], p2[2], axial_pen, radial_pen);
     return sp ? 0 : -1;
   }
   return sphere_sphere_raw(q1, s1[0], q2, s2[0], margin, c);

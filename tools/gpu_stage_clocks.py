@@ -10,13 +10,13 @@ env = ms.make("robot_planar_push", N, precision=prec, seed=0)
 env.reset(); _stagger_episodes(env, env.bundle.task.max_steps, 0)
 dev = torch.device("cuda:0")
 lo = torch.tensor([-0.2, -0.6], device=dev); hi = torch.tensor([0.2, -0.3], device=dev)
-acts = (lo + (hi - lo) * torch.rand(16, N, 2, device=dev)).float().contiguous()
-for i in range(300): env.step_flat(acts[i % 16])
+draw = lambda: (lo + (hi - lo) * torch.rand(N, 2, device=dev)).float()
+for i in range(550): env.step_flat(draw())  # a new batch every step: stationary state mix of the bench workload
 buf = (ctypes.c_longlong * (16 * N))()
 env._L.mjs_debug_times(env._h, buf, 16 * N)
 acc = np.zeros(12); tot = 0.0
 for rep in range(4):
-    env.step_flat(acts[rep]); torch.cuda.synchronize()
+    env.step_flat(draw()); torch.cuda.synchronize()
     env._L.mjs_debug_times(env._h, buf, 16 * N)
     t = np.frombuffer(buf, dtype=np.int64).reshape(N, 16).copy()
     acc += t[:, 4:16].mean(0); tot += ((t[:, 1] - t[:, 0]) * 1.965).mean()   # ns -> cycles at 1965 MHz
