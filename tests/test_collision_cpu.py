@@ -193,3 +193,35 @@ def test_mpr_penetration_vector_separates_random_pairs():
         assert np.dot(back[1], n) < -0.5
         assert convex_pair(t2, s2, p2, R2, t1, s1, p1 + back[1] * (back[0] + 2e-5), R1) is None
     assert hits > 150
+
+
+def test_side_side_cylinders_the_analytic_contact_is_the_convex_routines_contact():
+    """Bound on a stated deviation: upright cylinder pairs use an analytic side-side routine (depth r1 + r2 -
+    axis distance, horizontal normal, position at the middle of the axial overlap) where MuJoCo calls its convex solver.  For
+    parallel axes the general routine (include/mjs_convex.h, MuJoCo's MPR constants) must find the same depth and normal to its
+    own tolerance, and a position on the same contact line (the line is the whole axial overlap: any point of it is a valid
+    answer, the analytic routine picks its midpoint)."""
+    from oracle.oracle import convex_pair
+
+    CYL = 5
+    I = np.eye(3)
+    rng = np.random.RandomState(3)
+    worst_d = worst_n = 0.0
+    for _ in range(200):
+        r1, h1 = 0.02, 0.019
+        r2, h2 = (0.02, 0.019) if rng.rand() < 0.5 else (0.02, 0.05)
+        pen = rng.uniform(1e-5, 2e-3)
+        ang = rng.uniform(0, 2 * np.pi)
+        d = r1 + r2 - pen
+        p1 = np.array([0.0, 0.0, h1])
+        p2 = np.array([d * np.cos(ang), d * np.sin(ang), h2 + rng.uniform(0, 0.01)])
+        got = convex_pair(CYL, [r1, h1], p1, I, CYL, [r2, h2], p2, I)
+        assert got is not None
+        depth, n, p = got
+        worst_d = max(worst_d, abs(depth - pen))
+        worst_n = max(worst_n, np.abs(n - np.array([np.cos(ang), np.sin(ang), 0])).max())
+        lo, hi = max(p1[2] - h1, p2[2] - h2), min(p1[2] + h1, p2[2] + h2)
+        assert lo - 1e-6 <= p[2] <= hi + 1e-6                                   # on the axial overlap
+        mid = p1[:2] + (r1 - 0.5 * pen) * np.array([np.cos(ang), np.sin(ang)])  # half-way through the penetration
+        assert np.abs(p[:2] - mid).max() < 2e-5
+    assert worst_d < 2e-6 and worst_n < 2e-3, (worst_d, worst_n)
