@@ -293,21 +293,23 @@ int mjs_set_state(MjsSim* s, const MjsEnvState* h, int first, int count, int for
   int N = s->N;
   if (first < 0 || count < 0 || first + count > N) { mjs_set_error("mjs_set_state: range out of bounds"); return -1; }
   if (s->task.kind == MJS_TASK_POINTMASS) {
-    std::vector<double> sd((size_t)PM_NFIELD * N);
-    std::vector<int> si((size_t)PM_I_NFIELD * N);
-    MJS_CUDA_CHECK(cudaMemcpy(sd.data(), s->pm_sd, sd.size() * sizeof(double), cudaMemcpyDeviceToHost));
-    MJS_CUDA_CHECK(cudaMemcpy(si.data(), s->pm_si, si.size() * sizeof(int), cudaMemcpyDeviceToHost));
-    for (int i = 0; i < count; i++) {
-      int e = first + i;
-      const MjsEnvState& x = h[i];
-      sd[PM_QX * N + e] = x.qpos[0]; sd[PM_QY * N + e] = x.qpos[1]; sd[PM_VX * N + e] = x.qvel[0]; sd[PM_VY * N + e] = x.qvel[1];
-      sd[PM_MX * N + e] = x.mocap_pos[0]; sd[PM_MY * N + e] = x.mocap_pos[1]; sd[PM_WX * N + e] = x.qacc_warm[0]; sd[PM_WY * N + e] = x.qacc_warm[1];
-      sd[PM_TIME * N + e] = x.time; sd[PM_TX * N + e] = x.target[0]; sd[PM_TY * N + e] = x.target[1];
-      sd[PM_DIST * N + e] = x.dist; sd[PM_PDIST * N + e] = x.prev_dist; sd[PM_RET * N + e] = x.ep_return;
-      si[PM_I_EPISODE * N + e] = x.episode_id; si[PM_I_STATUS * N + e] = x.status; si[PM_I_STEPS * N + e] = x.episode_step;
+    // only the columns [first, first + count) of the field-major arrays travel (pitch = N elements)
+    const size_t C = (size_t)count;
+    if (C == 0) return 0;
+    std::vector<double> sd((size_t)PM_NFIELD * C);
+    std::vector<int> si((size_t)PM_I_NFIELD * C);
+    MJS_CUDA_CHECK(cudaMemcpy2D(sd.data(), C * sizeof(double), s->pm_sd + first, (size_t)N * sizeof(double), C * sizeof(double), PM_NFIELD, cudaMemcpyDeviceToHost));
+    MJS_CUDA_CHECK(cudaMemcpy2D(si.data(), C * sizeof(int), s->pm_si + first, (size_t)N * sizeof(int), C * sizeof(int), PM_I_NFIELD, cudaMemcpyDeviceToHost));
+    for (size_t e = 0; e < C; e++) {
+      const MjsEnvState& x = h[e];
+      sd[PM_QX * C + e] = x.qpos[0]; sd[PM_QY * C + e] = x.qpos[1]; sd[PM_VX * C + e] = x.qvel[0]; sd[PM_VY * C + e] = x.qvel[1];
+      sd[PM_MX * C + e] = x.mocap_pos[0]; sd[PM_MY * C + e] = x.mocap_pos[1]; sd[PM_WX * C + e] = x.qacc_warm[0]; sd[PM_WY * C + e] = x.qacc_warm[1];
+      sd[PM_TIME * C + e] = x.time; sd[PM_TX * C + e] = x.target[0]; sd[PM_TY * C + e] = x.target[1];
+      sd[PM_DIST * C + e] = x.dist; sd[PM_PDIST * C + e] = x.prev_dist; sd[PM_RET * C + e] = x.ep_return;
+      si[PM_I_EPISODE * C + e] = x.episode_id; si[PM_I_STATUS * C + e] = x.status; si[PM_I_STEPS * C + e] = x.episode_step;
     }
-    MJS_CUDA_CHECK(cudaMemcpy(s->pm_sd, sd.data(), sd.size() * sizeof(double), cudaMemcpyHostToDevice));
-    MJS_CUDA_CHECK(cudaMemcpy(s->pm_si, si.data(), si.size() * sizeof(int), cudaMemcpyHostToDevice));
+    MJS_CUDA_CHECK(cudaMemcpy2D(s->pm_sd + first, (size_t)N * sizeof(double), sd.data(), C * sizeof(double), C * sizeof(double), PM_NFIELD, cudaMemcpyHostToDevice));
+    MJS_CUDA_CHECK(cudaMemcpy2D(s->pm_si + first, (size_t)N * sizeof(int), si.data(), C * sizeof(int), C * sizeof(int), PM_I_NFIELD, cudaMemcpyHostToDevice));
     (void)forward;  // callers pass the warm start explicitly for PointMass
     return 0;
   }
@@ -320,20 +322,21 @@ int mjs_get_state(MjsSim* s, MjsEnvState* h, int first, int count) {
   int N = s->N;
   if (first < 0 || count < 0 || first + count > N) { mjs_set_error("mjs_get_state: range out of bounds"); return -1; }
   if (s->task.kind == MJS_TASK_POINTMASS) {
-    std::vector<double> sd((size_t)PM_NFIELD * N);
-    std::vector<int> si((size_t)PM_I_NFIELD * N);
-    MJS_CUDA_CHECK(cudaMemcpy(sd.data(), s->pm_sd, sd.size() * sizeof(double), cudaMemcpyDeviceToHost));
-    MJS_CUDA_CHECK(cudaMemcpy(si.data(), s->pm_si, si.size() * sizeof(int), cudaMemcpyDeviceToHost));
-    for (int i = 0; i < count; i++) {
-      int e = first + i;
-      MjsEnvState& x = h[i];
+    const size_t C = (size_t)count;
+    if (C == 0) return 0;
+    std::vector<double> sd((size_t)PM_NFIELD * C);
+    std::vector<int> si((size_t)PM_I_NFIELD * C);
+    MJS_CUDA_CHECK(cudaMemcpy2D(sd.data(), C * sizeof(double), s->pm_sd + first, (size_t)N * sizeof(double), C * sizeof(double), PM_NFIELD, cudaMemcpyDeviceToHost));
+    MJS_CUDA_CHECK(cudaMemcpy2D(si.data(), C * sizeof(int), s->pm_si + first, (size_t)N * sizeof(int), C * sizeof(int), PM_I_NFIELD, cudaMemcpyDeviceToHost));
+    for (size_t e = 0; e < C; e++) {
+      MjsEnvState& x = h[e];
       memset(&x, 0, sizeof(x));
-      x.qpos[0] = sd[PM_QX * N + e]; x.qpos[1] = sd[PM_QY * N + e]; x.qvel[0] = sd[PM_VX * N + e]; x.qvel[1] = sd[PM_VY * N + e];
-      x.mocap_pos[0] = sd[PM_MX * N + e]; x.mocap_pos[1] = sd[PM_MY * N + e]; x.qacc_warm[0] = sd[PM_WX * N + e]; x.qacc_warm[1] = sd[PM_WY * N + e];
-      x.time = sd[PM_TIME * N + e]; x.target[0] = sd[PM_TX * N + e]; x.target[1] = sd[PM_TY * N + e];
+      x.qpos[0] = sd[PM_QX * C + e]; x.qpos[1] = sd[PM_QY * C + e]; x.qvel[0] = sd[PM_VX * C + e]; x.qvel[1] = sd[PM_VY * C + e];
+      x.mocap_pos[0] = sd[PM_MX * C + e]; x.mocap_pos[1] = sd[PM_MY * C + e]; x.qacc_warm[0] = sd[PM_WX * C + e]; x.qacc_warm[1] = sd[PM_WY * C + e];
+      x.time = sd[PM_TIME * C + e]; x.target[0] = sd[PM_TX * C + e]; x.target[1] = sd[PM_TY * C + e];
       x.target[2] = s->task.target_lo[2];
-      x.dist = sd[PM_DIST * N + e]; x.prev_dist = sd[PM_PDIST * N + e]; x.ep_return = sd[PM_RET * N + e];
-      x.episode_id = si[PM_I_EPISODE * N + e]; x.status = si[PM_I_STATUS * N + e]; x.episode_step = si[PM_I_STEPS * N + e];
+      x.dist = sd[PM_DIST * C + e]; x.prev_dist = sd[PM_PDIST * C + e]; x.ep_return = sd[PM_RET * C + e];
+      x.episode_id = si[PM_I_EPISODE * C + e]; x.status = si[PM_I_STATUS * C + e]; x.episode_step = si[PM_I_STEPS * C + e];
     }
     return 0;
   }

@@ -87,3 +87,31 @@ def test_c_abi_error_returns():
         env.step(torch.zeros(8, 3).cuda())                          # wrong action width (point_reach.py:158)
     assert env._L.mjs_num_envs(env._h) == 8 and env._L.mjs_obs_dim(env._h) == 4 and env._L.mjs_action_dim(env._h) == 2
     env.close()
+
+
+def test_pointmass_state_ranges_travel_alone():
+    """mjs_get_state / mjs_set_state of a sub-range of a PointMass batch move only that range (strided copies of the
+    field-major arrays): the range reads back what was written, its neighbours are untouched."""
+    import mujoco_sim_b200 as ms
+
+    n = 1000
+    env = ms.make("point_mass_reach", n, precision="f64", seed=3)
+    env.reset()
+    env.step(None)
+    before = env.get_state()
+    first, count = 333, 77
+    sub = env.get_state(first, count)
+    for i in range(count):
+        assert sub[i].qpos[0] == before[first + i].qpos[0] and sub[i].episode_step == before[first + i].episode_step
+        sub[i].qpos[0] = 0.001 * i; sub[i].qvel[1] = -0.002 * i; sub[i].target[0] = 0.01; sub[i].episode_step = 7
+    env.set_state(sub, first=first, forward=False)
+    after = env.get_state()
+    for e in range(n):
+        if first <= e < first + count:
+            i = e - first
+            assert after[e].qpos[0] == 0.001 * i and after[e].qvel[1] == -0.002 * i and after[e].target[0] == 0.01 and after[e].episode_step == 7
+            assert after[e].qpos[1] == before[e].qpos[1] and after[e].time == before[e].time
+        else:
+            assert bytes(after[e]) == bytes(before[e])
+    assert len(env.get_state(n, 0)) == 0
+    env.close()
