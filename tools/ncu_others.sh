@@ -9,6 +9,7 @@ cap() {  # name, kernel regex, bench args
   ncu -i /tmp/o_$T.ncu-rep --page raw --csv > gpurun_out/prof_${T}_raw.csv 2>/dev/null
 }
 cap pointmass_f64 pm_step_kernel --workload point_mass_reach
+ncu -i /tmp/o_pointmass_f64.ncu-rep --page source --csv > gpurun_out/prof_pointmass_f64_source.csv 2>/dev/null
 cap reach_f64 arm_step_kernel --workload robot_reach
 cap button_f64 arm_step_kernel --workload push_button
 cap push_mixed arm_step_kernel --workload planar_push --precision mixed
