@@ -158,7 +158,12 @@ template <> __device__ __forceinline__ void sincos_r<double>(double x, double* s
 template <typename real> __device__ __forceinline__ real rsqrt_r(real x);
 template <> __device__ __forceinline__ float rsqrt_r<float>(float x) { return rsqrtf(x); }
 // rsqrt(double): MUFU.RSQ64H seed + Newton steps (~1 ulp), a quarter of the instructions of 1.0 / sqrt(x)
+#ifdef MJS_RSQRT_NOINLINE  // A/B: one shared copy of the ~25-instruction sequence instead of one per call site (hot code -3.7 KB)
+static __device__ __noinline__ double rsqrt_shared(double x) { return rsqrt(x); }
+template <> __device__ __forceinline__ double rsqrt_r<double>(double x) { return rsqrt_shared(x); }
+#else
 template <> __device__ __forceinline__ double rsqrt_r<double>(double x) { return rsqrt(x); }
+#endif
 
 template <typename real>
 __device__ __forceinline__ void cross3(real* r, const real* a, const real* b) {
