@@ -36,10 +36,22 @@ def _ptr(t: Optional[torch.Tensor]):
     return ctypes.c_void_p(t.data_ptr()) if t is not None else None
 
 
+STATE_OBS, VISUAL_OBS = "state_observations", "visual_observations"
+# observation_type="visual_observations": what each task enables besides its camera(s)
+# (point_reach.py:115-123, robot_reach.py:134-141, robot_planar_push.py:134-142, robot_push_button.py:108-124) and the
+# observable names of the camera entities (entities/camera.py:153-160; the wrist camera is renamed at robot_push_button.py:95).
+_VISUAL = {
+    "point_mass_reach": (["pointmass/position"], [("Camera/rgb_image", "top_down")]),
+    "robot_reach": (["ur5e/tcp_position"], [("Camera/rgb_image", "front_tilted")]),
+    "robot_planar_push": (["ur5e/tcp_position"], [("Camera/rgb_image", None)]),  # None: the config's camera (first of the bundle)
+    "robot_push_button": (["ur5e/joint_configuration"], [("Camera/rgb_image", "scene"), ("ur5e/Camera/wrist_camera_rgb_image", "wrist")]),
+}
+
+
 class BatchedMujocoSimEnv:
     def __init__(self, task_name: str, num_envs: int, device="cuda:0", seed: int = 0, env_offset: int = 0,
                  precision: str = "f64", autoreset: bool = True, solver_tolerance: Optional[float] = None, obs_dtype: str = "float32",
-                 **task_kwargs):
+                 observation_type: str = STATE_OBS, image_resolution: Optional[int] = None, **task_kwargs):
         if not torch.cuda.is_available():
             raise _lib.MjsimError("BatchedMujocoSimEnv needs a CUDA device (there is no CPU fallback)")
         self.bundle = _BUILDERS[task_name](**task_kwargs)
@@ -76,6 +88,19 @@ class BatchedMujocoSimEnv:
             _lib.check(self._L.mjs_set_output64(self._h, _ptr(self._obs64), _ptr(self._reward64), _ptr(self._final_obs64)))
         self.seed_value = int(seed)
         self.obs_keys = list(self.bundle.obs_keys)
+        # visual observations: the task's camera image(s), ray-cast on the device after every step / reset (mjs_render), next to the
+        # state observables the reference keeps enabled in that mode.  The kernels still produce the full state vector.
+        assert observation_type in (STATE_OBS, VISUAL_OBS), observation_type
+        self.observation_type = observation_type
+        self.image_keys = []  # [(observation key, camera name, (H, W, 3))]
+        if observation_type == VISUAL_OBS:
+            keep, cams = _VISUAL[task_name]
+            self._visual_keep = [k for k, _ in self.obs_keys if k in keep]
+            res = int(image_resolution or self.bundle.image_resolution)
+            for key, cam in cams:
+                cam = cam if cam is not None else next(iter(self.bundle.cameras))
+                self.image_keys.append((key, cam, (res, res, 3)))
+            self._images = {key: torch.zeros(N, res, res, 3, dtype=torch.uint8, device=self.device) for key, _, _ in self.image_keys}
         self.has_success = task_name in ("point_mass_reach", "robot_push_button")
         self.single_action_low = self.bundle.action_low
         self.single_action_high = self.bundle.action_high
@@ -84,11 +109,16 @@ class BatchedMujocoSimEnv:
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
-    def _obs_dict(self, flat: torch.Tensor):
+    def _obs_dict(self, flat: torch.Tensor, images: bool = True):
         out, k = {}, 0
         for key, dim in self.obs_keys:
             out[key] = flat[:, k : k + dim]
             k += dim
+        if self.observation_type == VISUAL_OBS:
+            out = {key: out[key] for key in self._visual_keep}
+            if images:  # of the CURRENT device state (after an auto-reset: the new episode's first frame, like the reference's reset obs)
+                for key, cam, shape in self.image_keys:
+                    out[key] = self.render(cam, shape[1], shape[0], out=self._images[key])
         return out
 
     def close(self):
@@ -145,7 +175,8 @@ class BatchedMujocoSimEnv:
         if self.has_success:
             info["is_success"] = f[:, 2].float()
         if self.autoreset:
-            info["final_observation"] = self._obs_dict(self.final_observation)
+            # visual mode: the terminal frame is gone once the kernel has reset the env in the same launch -- state keys only
+            info["final_observation"] = self._obs_dict(self.final_observation, images=False)
             info["_final_observation"] = f[:, 3].bool()
         return self._obs_dict(self.observation), self.reward, f[:, 0].bool(), f[:, 1].bool(), info
 

@@ -59,11 +59,17 @@ def single_observation_space(env: BatchedMujocoSimEnv, flatten: bool = False):
     """dmc2gym.py:93-101 -- Dict of unbounded Boxes per observable in the spec dtype (float64 in the reference: make the
     env with obs_dtype="float64"; the default here is float32), or one flat float32 Box when flatten_observation_space=True
     (dmc2gym.py:66-75 casts the flattened observation to float32)."""
+    visual = getattr(env, "observation_type", "state_observations") == "visual_observations"
     if flatten:
+        if visual:
+            raise ValueError("flatten_observation_space needs state observations (dmc2gym.py:93-98 flattens vectors, not images)")
         n = sum(d for _, d in env.obs_keys)
         return _box(np.full(n, -np.inf), np.full(n, np.inf), np.float32)
     dt = np.float64 if getattr(env, "obs_dtype", "float32") == "float64" else np.float32
-    spaces = {k: _box(np.full(d, -np.inf), np.full(d, np.inf), dt) for k, d in env.obs_keys}
+    spaces = {k: _box(np.full(d, -np.inf), np.full(d, np.inf), dt) for k, d in env.obs_keys if not visual or k in env._visual_keep}
+    if visual:  # entities/camera.py:124-150: uint8 image observable, channel-last
+        for key, _, shape in env.image_keys:
+            spaces[key] = _box(np.zeros(shape), np.full(shape, 255), np.uint8)
     try:
         import gymnasium
 
@@ -96,11 +102,16 @@ class _HostBuffers:
         p = lambda x: x.ctypes.data_as(ctypes.c_void_p)
         _lib.check(env._L.mjs_step_host(env._h, p(actions), p(self.obs), p(self.rew), p(self.flags), p(self.final), 1))
 
-    def split(self, env, flat):
+    def split(self, env, flat, images: bool = True):
         out, k = {}, 0
         for key, dim in env.obs_keys:
             out[key] = flat[:, k : k + dim].copy()
             k += dim
+        if getattr(env, "observation_type", "state_observations") == "visual_observations":
+            out = {key: out[key] for key in env._visual_keep}
+            if images and len(flat) == env.num_envs:  # frames of the current device state (not for single terminal rows)
+                for key, cam, shape in env.image_keys:
+                    out[key] = env.render(cam, shape[1], shape[0], out=env._images[key]).cpu().numpy()
         return out
 
 
@@ -143,7 +154,7 @@ class SB3VecEnvFacade:
         for i in np.nonzero(dones)[0].tolist():
             info = dict(shared[code[i]])
             t = b.final[i : i + 1]
-            info["terminal_observation"] = t[0].copy() if self.flatten else {k: v[0] for k, v in b.split(e, t).items()}
+            info["terminal_observation"] = t[0].copy() if self.flatten else {k: v[0] for k, v in b.split(e, t, images=False).items()}
             info["TimeLimit.truncated"] = bool(f[i, 1]) and not bool(f[i, 0])
             infos[i] = info
         return self._obs(b.obs), b.rew.copy(), dones, infos
@@ -218,7 +229,7 @@ class GymnasiumVectorFacade:
         b.step(e, a)
         f = b.flags
         info = {"discount": 1.0 - f[:, 0].astype(np.float32), "_final_observation": f[:, 3].astype(bool),
-                "final_observation": self._obs(b.final)}
+                "final_observation": b.final.copy() if self.flatten else b.split(e, b.final, images=False)}
         if e.has_success:
             info["is_success"] = f[:, 2].astype(np.float32)
         return self._obs(b.obs), b.rew.copy(), f[:, 0].astype(bool), f[:, 1].astype(bool), info
@@ -227,8 +238,11 @@ class GymnasiumVectorFacade:
         self.env.close()
 
 
-# gym ids in the style of /root/reference/mujoco_sim/__init__.py:26-40 (state observations)
+# gym ids: the two the reference registers (/root/reference/mujoco_sim/__init__.py:26-40, both with visual observations) and a
+# state-observation id per task in the same style
 REGISTRY = {
+    "mujoco_sim/point_mass_reach-v0": ("point_mass_reach", {"observation_type": "visual_observations", "image_resolution": 64}),
+    "mujoco_sim/robot_push_button_visual-v0": ("robot_push_button", {"observation_type": "visual_observations", "image_resolution": 96}),
     "mujoco_sim/point_mass_reach_state-v0": ("point_mass_reach", {}),
     "mujoco_sim/robot_reach_state-v0": ("robot_reach", {}),
     "mujoco_sim/robot_planar_push_state-v0": ("robot_planar_push", {}),

@@ -63,3 +63,52 @@ def test_render_argument_checks_and_custom_resolution():
     with pytest.raises(lib.MjsimError, match="bad image size"):
         env.render(width=5000, height=8)
     env.close()
+
+
+@pytest.mark.parametrize("task", ["point_mass_reach", "robot_reach", "robot_planar_push", "robot_push_button"])
+def test_visual_observation_type_returns_the_cameras_and_the_enabled_state_keys(task):
+    """observation_type="visual_observations" (point_reach.py:119-121, robot_reach.py:139-141, robot_planar_push.py:140-142,
+    robot_push_button.py:121-124): the observation holds the camera image(s) of the state the step ended in, plus the state
+    observables the reference keeps enabled; everything else (reward, flags, state keys' values) equals the state-observation env."""
+    import torch
+
+    import mujoco_sim_b200 as ms
+    from mujoco_sim_b200.envs import _VISUAL
+
+    n = 6
+    ev = ms.make(task, n, seed=11, observation_type="visual_observations")
+    es = ms.make(task, n, seed=11)
+    ov, _ = ev.reset(); os_, _ = es.reset()
+    keep, cams = _VISUAL[task]
+    assert list(ov) == keep + [k for k, _ in cams]
+    for _ in range(3):
+        ov, rv, tv, trv, iv = ev.step(None); os_, rs, ts, trs, is_ = es.step(None)
+        assert torch.equal(rv, rs) and torch.equal(tv, ts) and torch.equal(trv, trs)
+        for k in keep:
+            assert torch.equal(ov[k], os_[k])
+        for key, cam, shape in ev.image_keys:
+            img = ov[key]
+            assert img.dtype == torch.uint8 and tuple(img.shape) == (n,) + shape
+            assert torch.equal(img, es.render(cam, shape[1], shape[0]))      # the frame of the state the step ended in
+            assert img.float().std() > 1                                    # not a blank frame
+        assert set(iv["final_observation"]) == set(keep)                    # terminal frames are not kept (state keys only)
+    ev.close(); es.close()
+
+
+def test_reference_gym_ids_are_visual_envs():
+    """mujoco_sim/__init__.py:26-40 registers two ids, both with visual observations (64 and 96 pixels)."""
+    from mujoco_sim_b200 import vecenv
+
+    v = vecenv.make_vec("mujoco_sim/point_mass_reach-v0", 4)
+    obs, _ = v.reset(seed=2025)
+    assert obs["Camera/rgb_image"].shape == (4, 64, 64, 3) and obs["Camera/rgb_image"].dtype == np.uint8 and obs["pointmass/position"].shape == (4, 2)
+    obs2, rew, term, trunc, info = v.step(np.zeros((4, 2), np.float32))
+    assert obs2["Camera/rgb_image"].shape == (4, 64, 64, 3) and set(info["final_observation"]) == {"pointmass/position"}
+    assert v.single_observation_space.spaces["Camera/rgb_image"].shape == (64, 64, 3)
+    obs3, _ = v.reset(seed=2025)
+    assert np.array_equal(obs3["Camera/rgb_image"], obs["Camera/rgb_image"])  # test/test_gym_envs.py:21-36 on the image observation
+    v.close()
+    b = vecenv.make_vec("mujoco_sim/robot_push_button_visual-v0", 2, api="sb3")
+    o = b.reset()
+    assert o["Camera/rgb_image"].shape == (2, 96, 96, 3) and o["ur5e/Camera/wrist_camera_rgb_image"].shape == (2, 96, 96, 3) and o["ur5e/joint_configuration"].shape == (2, 6)
+    b.close()

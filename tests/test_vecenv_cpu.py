@@ -29,6 +29,23 @@ def test_spaces_follow_the_reference_adapter():
 
 
 def test_registry_names_every_task():
-    assert sorted(t for t, _ in vecenv.REGISTRY.values()) == ["point_mass_reach", "robot_planar_push", "robot_push_button", "robot_reach"]
+    state = {k: v for k, v in vecenv.REGISTRY.items() if k.endswith("_state-v0")}
+    assert sorted(t for t, _ in state.values()) == ["point_mass_reach", "robot_planar_push", "robot_push_button", "robot_reach"]
+    # the reference's own two ids (mujoco_sim/__init__.py:26-40), both visual
+    assert vecenv.REGISTRY["mujoco_sim/point_mass_reach-v0"] == ("point_mass_reach", {"observation_type": "visual_observations", "image_resolution": 64})
+    assert vecenv.REGISTRY["mujoco_sim/robot_push_button_visual-v0"][1]["image_resolution"] == 96
     for k in vecenv.REGISTRY:
-        assert k.startswith("mujoco_sim/") and k.endswith("_state-v0")
+        assert k.startswith("mujoco_sim/") and k.endswith("-v0")
+
+
+def test_visual_observation_spaces():
+    b = T.build_pointmass_reach()
+    e = _stub(b)
+    e.observation_type = "visual_observations"; e._visual_keep = ["pointmass/position"]; e.image_keys = [("Camera/rgb_image", "top_down", (64, 64, 3))]
+    o = vecenv.single_observation_space(e)
+    assert list(o.spaces) == ["pointmass/position", "Camera/rgb_image"]  # point_reach.py:119-121
+    img = o.spaces["Camera/rgb_image"]
+    assert img.shape == (64, 64, 3) and img.dtype == np.uint8 and img.high.max() == 255
+    import pytest
+    with pytest.raises(ValueError):
+        vecenv.single_observation_space(e, flatten=True)
