@@ -133,11 +133,15 @@ class BatchedMujocoSimEnv:
             pass
 
     # ---------------------------------------------------------------------- API
-    def reset(self, seed: Optional[int] = None, env_mask: Optional[torch.Tensor] = None):
-        """dmc2gym.py:157-163 for every env (or the masked ones)."""
+    def reset(self, seed: Optional[int] = None, env_mask: Optional[torch.Tensor] = None, env_ids=None):
+        """dmc2gym.py:157-163 for every env, or for the envs selected by a boolean `env_mask` [N] / a list of `env_ids`."""
         if seed is not None:  # dmc2gym.py:157-160: reset(seed=s) re-seeds the live env first
             self.seed(seed)
         mask = None
+        if env_ids is not None:
+            assert env_mask is None, "give env_mask or env_ids, not both"
+            env_mask = torch.zeros(self.num_envs, dtype=torch.uint8, device=self.device)
+            env_mask[torch.as_tensor(env_ids, dtype=torch.long, device=self.device)] = 1
         if env_mask is not None:
             mask = env_mask.to(device=self.device, dtype=torch.uint8).contiguous()
         _lib.check(self._L.mjs_reset(self._h, _ptr(mask), _ptr(self._obs), self._stream()))
@@ -219,6 +223,27 @@ class BatchedMujocoSimEnv:
         arr = (MjsVisual * max(len(vis), 1))(*vis)
         _lib.check(self._L.mjs_render(self._h, ctypes.byref(cam), arr, len(vis), w, h, _ptr(out), self._stream()))
         return out
+
+    # spaces and facades: same objects the vector-env wrappers expose
+    @property
+    def single_action_space(self):
+        from . import vecenv
+        return vecenv.single_action_space(self)
+
+    @property
+    def single_observation_space(self):
+        from . import vecenv
+        return vecenv.single_observation_space(self)
+
+    def as_sb3_vecenv(self, flatten_observation_space: bool = False):
+        """stable_baselines3 VecEnv protocol over this env (numpy in / out, `terminal_observation`, `TimeLimit.truncated`)."""
+        from . import vecenv
+        return vecenv.SB3VecEnvFacade(self, flatten_observation_space)
+
+    def as_gymnasium_vector_env(self, flatten_observation_space: bool = False):
+        """gymnasium.vector.VectorEnv protocol over this env (same-step autoreset, batched info arrays)."""
+        from . import vecenv
+        return vecenv.GymnasiumVectorFacade(self, flatten_observation_space)
 
     def join_aux(self):
         """Make the current stream wait for background reset preparation in flight."""

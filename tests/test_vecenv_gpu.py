@@ -54,3 +54,31 @@ def test_gymnasium_facade_matches_device_api():
         np.testing.assert_array_equal(info["is_success"], i2["is_success"].cpu().numpy())
         assert (info["_final_observation"] == (term | trunc)).all()
     v.close(); e.close()
+
+
+def test_env_ids_reset_and_facade_shortcuts():
+    """SURVEY.md 8b exports: reset(env_ids=...), single_*_space on the env, as_sb3_vecenv() / as_gymnasium_vector_env()."""
+    import torch
+
+    import mujoco_sim_b200 as ms
+
+    env = ms.make("point_mass_reach", 8, seed=5)
+    env.reset()
+    for _ in range(3):
+        env.step(None)
+    before = env.get_state()
+    obs, _ = env.reset(env_ids=[1, 6])
+    after = env.get_state()
+    for e in range(8):
+        if e in (1, 6):
+            assert after[e].episode_step == 0 and after[e].episode_id == before[e].episode_id + 1
+        else:
+            assert bytes(after[e]) == bytes(before[e])
+    assert env.single_action_space.shape == (2,) and list(env.single_observation_space.spaces) == ["pointmass/position", "goal_position"]
+    v = env.as_gymnasium_vector_env()
+    o, r, t, tr, info = v.step(np.zeros((8, 2), np.float32))
+    assert o["pointmass/position"].shape == (8, 2) and r.shape == (8,)
+    s = env.as_sb3_vecenv()
+    o2, r2, d2, infos = s.step(np.zeros((8, 2), np.float32))
+    assert len(infos) == 8 and d2.shape == (8,)
+    env.close()
