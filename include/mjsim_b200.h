@@ -90,6 +90,12 @@ int mjs_get_state(MjsSim* sim, MjsEnvState* h_states, int first, int count);
 int mjs_stats_device(MjsSim* sim, double** d_out);
 int mjs_stats(MjsSim* sim, double* h_out8, int reset);
 
+/* Per-env status words (MJS_STATUS_* bits of include/mjs_model.h: non-finite state, IK unreachable -- the reference's
+ * ValueError("IK failed"), robots/robot.py:221-224 --, contact overflow, unsupported geom pair) copied into the caller's
+ * device buffer d_status[num_envs] on `stream`; no host synchronisation.  Python exceptions of the reference become these
+ * bits: device code never throws. */
+int mjs_status(MjsSim* sim, int* d_status, void* stream);
+
 /* Planar Push prepares the next episode of finished envs (sampling + 150 settle
  * steps) on an internal low-priority stream.  mjs_join_aux makes `stream` wait for
  * whatever of that work is in flight (used to close a timed region). */

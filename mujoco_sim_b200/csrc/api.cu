@@ -474,6 +474,17 @@ int mjs_reseed(MjsSim* s, unsigned long long seed) {
 
 int mjs_stats_device(MjsSim* s, double** d_out) { *d_out = s->d_stats; return 0; }
 
+int mjs_status(MjsSim* s, int* d_status, void* stream) {
+  DeviceGuard guard(s->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!d_status) { mjs_set_error("mjs_status: d_status is NULL"); return -1; }
+  if (s->task.kind == MJS_TASK_POINTMASS) {  // field-major: the status column is contiguous
+    MJS_CUDA_CHECK(cudaMemcpyAsync(d_status, s->pm_si + (size_t)PM_I_STATUS * s->N, sizeof(int) * (size_t)s->N, cudaMemcpyDeviceToDevice, st));
+    return 0;
+  }
+  return arm_status(s->arm, d_status, st);
+}
+
 int mjs_stats(MjsSim* s, double* h_out8, int reset) {
   DeviceGuard guard(s->device);
   MJS_CUDA_CHECK(cudaDeviceSynchronize());

@@ -184,6 +184,14 @@ int arm_poses(ArmSim* a, float* d_gpose, float* d_aux, cudaStream_t st) {
   return dispatch(a, 6, io, st);
 }
 
+// mjs_status: the status column of the env-major integer records, gathered into the caller's buffer on its stream
+int arm_status(ArmSim* a, int* d_status, cudaStream_t st) {
+  const int I_STATUS = 5;  // ArmLayout<NOBJ>::I_STATUS (same index for every NOBJ)
+  static_assert(ArmLayout<0>::I_STATUS == 5 && ArmLayout<3>::I_STATUS == 5, "status column moved");
+  MJS_CUDA_CHECK(cudaMemcpy2DAsync(d_status, sizeof(int), a->si + I_STATUS, sizeof(int) * (size_t)a->SI, sizeof(int), (size_t)a->N, cudaMemcpyDeviceToDevice, st));
+  return 0;
+}
+
 void arm_set_output64(ArmSim* a, double* d_obs64, double* d_reward64, double* d_final_obs64) {
   a->obs64 = d_obs64; a->reward64 = d_reward64; a->final_obs64 = d_final_obs64;
 }

@@ -20,3 +20,4 @@ int arm_step_noalloc(ArmSim* a, const float* d_actions, float* d_obs, float* d_r
 void arm_set_output64(ArmSim* a, double* d_obs64, double* d_reward64, double* d_final_obs64);
 int arm_reseed(ArmSim* a, unsigned long long seed);
 int arm_poses(ArmSim* a, float* d_gpose, float* d_aux, cudaStream_t st);
+int arm_status(ArmSim* a, int* d_status, cudaStream_t st);

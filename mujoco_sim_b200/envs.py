@@ -260,6 +260,14 @@ class BatchedMujocoSimEnv:
         _lib.check(self._L.mjs_get_state(self._h, arr, first, count))
         return arr
 
+    def status(self) -> torch.Tensor:
+        """Per-env status words (MJS_STATUS_* bits: non-finite state, IK unreachable, contact overflow, unsupported pair) as an
+        int32 device tensor [N]; the reference raises Python exceptions instead (robots/robot.py:221-224)."""
+        if not hasattr(self, "_status"):
+            self._status = torch.zeros(self.num_envs, dtype=torch.int32, device=self.device)
+        _lib.check(self._L.mjs_status(self._h, _ptr(self._status), self._stream()))
+        return self._status
+
     def stats(self, reset: bool = True):
         out = (ctypes.c_double * 8)()
         _lib.check(self._L.mjs_stats(self._h, out, int(reset)))

@@ -42,6 +42,7 @@ _SIGS = {
     "mjs_destroy": (None, [ctypes.c_void_p]),
     "mjs_reset": (ctypes.c_int, [ctypes.c_void_p] * 4),
     "mjs_step": (ctypes.c_int, [ctypes.c_void_p] * 6 + [ctypes.c_int, ctypes.c_void_p]),
+    "mjs_status": (ctypes.c_int, [ctypes.c_void_p] * 3),
     "mjs_step_noalloc": (ctypes.c_int, [ctypes.c_void_p] * 6 + [ctypes.c_int, ctypes.c_void_p]),
     "mjs_reseed": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_ulonglong]),
     "mjs_set_output64": (ctypes.c_int, [ctypes.c_void_p] * 4),

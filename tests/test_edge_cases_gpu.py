@@ -50,7 +50,13 @@ def test_unreachable_action_sets_the_ik_status_bit_like_the_oracle():
     np.testing.assert_array_equal(gpu != 0, cpu != 0)
     assert (gpu[1::2] != 0).all() and (gpu[::2] == 0).all()
     assert np.abs(q - ora.field("qpos", 27)).max() < 1e-6   # the previous target is held
+    # the same words through mjs_status (device buffer, no host round trip of the state)
+    np.testing.assert_array_equal(env.status().cpu().numpy(), np.array([s.status for s in st]))
     env.close()
+    import mujoco_sim_b200 as ms
+    pm = ms.make("point_mass_reach", 33, seed=1); pm.reset(); pm.step(None)
+    assert pm.status().shape == (33,) and int(pm.status().abs().sum()) == 0
+    pm.close()
 
 
 def test_masked_reset_only_touches_the_masked_envs():
