@@ -2185,15 +2185,20 @@ struct ArmTask {
       else reward = (-sum / NOBJ - A.nearest_coef * nearest) * 0.1;
       accomplished = within == NOBJ;
     } else {  // BUTTON
-#pragma unroll
-      for (int k = 0; k < 6; k++) o.obs[k] = W.qpos[k];
+      // robot_push_button.py:109-113: joint_configuration with ABS_JOINT_ACTION (7 actions), tcp_position with ABS_EEF_ACTION (4)
+      const bool joint_action = A.action_dim == 7;
       const real* R = W.xmat[A.touch_slot];
       real tp[3] = {A.touch_pos[0], A.touch_pos[1], A.touch_pos[2]}, v[3];
       mat_vec(v, R, tp);
       double quirk = 0.5 * ((double)A.touch_size[0] / 1.01);  // switch.py:86-87
+      double swp[3];
 #pragma unroll
-      for (int k = 0; k < 3; k++) o.obs[6 + k] = (double)W.xpos[A.touch_slot][k] + (double)v[k] + quirk;
-      o.obs[9] = T.swa;
+      for (int k = 0; k < 3; k++) swp[k] = (double)W.xpos[A.touch_slot][k] + (double)v[k] + quirk;
+#pragma unroll
+      for (int k = 0; k < 6; k++) o.obs[k] = joint_action ? W.qpos[k] : (k < 3 ? tcp[k] : swp[k - 3]);
+#pragma unroll
+      for (int k = 0; k < 3; k++) o.obs[6 + k] = joint_action ? swp[k] : (k == 0 ? (double)T.swa : 0.0);
+      o.obs[9] = joint_action ? (double)T.swa : 0.0;
       double dg = sqrt((tcp[0] - A.button_goal[0]) * (tcp[0] - A.button_goal[0]) + (tcp[1] - A.button_goal[1]) * (tcp[1] - A.button_goal[1]) + (tcp[2] - A.button_goal[2]) * (tcp[2] - A.button_goal[2]));
       bool goal = T.swa && dg < A.button_goal_radius;
       reward = goal ? 1.0 : 0.0;
@@ -2319,6 +2324,11 @@ struct ArmTask {
     for (int k = 0; k < 3; k++) { d[k] = goal[k] - tcp[k]; m = fmax(m, fabs(d[k])); }
     if (m > lim) for (int k = 0; k < 3; k++) d[k] = d[k] * 0.5 / m * A.control_dt;
     double tgt[3] = {tcp[0] + d[0], tcp[1] + d[1], tcp[2] + d[2]}, seed[6], q[6];
+    if (A.action_dim != 7) {  // ABS_EEF_ACTION: the Cartesian target itself + the closed gripper (robot_push_button.py:289-297)
+      for (int k = 0; k < 3; k++) action[k] = tgt[k];
+      action[3] = 0.0;
+      return true;
+    }
     for (int i = 0; i < 6; i++) seed[i] = W.qpos[i];
     bool ok = tcp_to_joints(A, tgt, seed, q, lane);
     for (int i = 0; i < 6; i++) action[i] = ok ? q[i] : seed[i];
@@ -2509,7 +2519,7 @@ __device__ __noinline__ void arm_step_env(const ArmModel<real>& A, WarpMem<real,
         Philox4 r = philox4x32_10(genv, io.step_index, MJS_RNG_ACTION, k >> 1, (uint32_t)io.seed, (uint32_t)(io.seed >> 32));
         double u = (k & 1) ? u53(r.v[2], r.v[3]) : u53(r.v[0], r.v[1]);
         action[k] = A.action_lo[k] + (A.action_hi[k] - A.action_lo[k]) * u;
-        if (A.kind == MJS_TASK_BUTTON && k < 6) action[k] = fmin(fmax(W.qpos[k] + action[k], -3.14), 3.14);
+        if (A.kind == MJS_TASK_BUTTON && A.action_dim == 7 && k < 6) action[k] = fmin(fmax(W.qpos[k] + action[k], -3.14), 3.14);
       }
     }
   }

@@ -44,7 +44,8 @@ _VISUAL = {
     "point_mass_reach": (["pointmass/position"], [("Camera/rgb_image", "top_down")]),
     "robot_reach": (["ur5e/tcp_position"], [("Camera/rgb_image", "front_tilted")]),
     "robot_planar_push": (["ur5e/tcp_position"], [("Camera/rgb_image", None)]),  # None: the config's camera (first of the bundle)
-    "robot_push_button": (["ur5e/joint_configuration"], [("Camera/rgb_image", "scene"), ("ur5e/Camera/wrist_camera_rgb_image", "wrist")]),
+    "robot_push_button": (["ur5e/joint_configuration", "ur5e/tcp_position"],  # whichever the action type enables (robot_push_button.py:109-113)
+                          [("Camera/rgb_image", "scene"), ("ur5e/Camera/wrist_camera_rgb_image", "wrist")]),
 }
 
 

@@ -389,9 +389,15 @@ def build_robot_reach(config: RobotReachConfig | None = None, obstacle: dict | N
                       visuals=vis, cameras={"front_tilted": _camera((0.0, -1.1, 0.5), (-0.7, -0.35, 0, 0.0), 70)}, image_resolution=96)  # :52
 
 
-def build_push_button(max_steps: int = 100, button_disturbances: bool = False) -> TaskBundle:
+ABS_EEF_ACTION, ABS_JOINT_ACTION = "absolute_eef_action", "absolute_joint_action"  # robot_push_button.py:29-30
+
+
+def build_push_button(max_steps: int = 100, button_disturbances: bool = False, action_type: str = ABS_JOINT_ACTION) -> TaskBundle:
     """RobotPushButtonTask scene (robot_push_button.py:56-119, props/switch.py:17-41),
-    state observations, ABS_JOINT_ACTION; rigid gripper.  button_disturbances
+    state observations; rigid gripper (the gripper channel of the action is accepted and ignored).
+    action_type (robot_push_button.py:143-157,172-203): ABS_JOINT_ACTION -- 6 joint targets + gripper through servoJ, observation
+    joint_configuration; ABS_EEF_ACTION -- TCP position in the robot workspace + gripper through servoL (top-down), observation
+    tcp_position.  button_disturbances
     (robot_push_button.py:56,159-165): an active, unpressed switch deactivates with probability 0.01 per control step."""
     world = S.Body("world")
     _arena_plane(world)
@@ -407,9 +413,11 @@ def build_push_button(max_steps: int = 100, button_disturbances: bool = False) -
     t = MjsTask()
     t.kind = MACROS["MJS_TASK_BUTTON"]
     _robot_task_common(t, comp, 0.1, 0.005, (0, 0, 0.174))
+    assert action_type in (ABS_EEF_ACTION, ABS_JOINT_ACTION), action_type
+    eef = action_type == ABS_EEF_ACTION
     t.reward_type = 0
-    t.action_dim = 7
-    t.obs_dim = 10
+    t.action_dim = 4 if eef else 7
+    t.obs_dim = 7 if eef else 10
     t.time_limit = max_steps * 0.1  # mujoco_sim/__init__.py:21,34
     t.set("spawn_lo", (-0.2, -0.6, 0.02)); t.set("spawn_hi", (0.2, -0.3, 0.3))
     t.set("target_lo", (-0.2, -0.6, 0.0)); t.set("target_hi", (0.2, -0.3, 0.1))
@@ -419,8 +427,14 @@ def build_push_button(max_steps: int = 100, button_disturbances: bool = False) -
     t.button_disturbances = int(bool(button_disturbances))
     t.disturb_prob = 0.01
     # synthetic rollouts: q_now +- 0.05 rad handled on device; box kept for the gripper dof
-    t.set("action_lo", [-0.05] * 6 + [0.0]); t.set("action_hi", [0.05] * 6 + [0.085])
-    keys = [("ur5e/joint_configuration", 6), ("unnamed_model/position", 3), ("unnamed_model/active", 1)]
+    if eef:  # synthetic rollouts: uniform over the action spec = the robot workspace (robot_push_button.py:78,176-192)
+        t.set("action_lo", [-0.2, -0.6, 0.02, 0.0]); t.set("action_hi", [0.2, -0.3, 0.3, 0.085])
+        keys = [("ur5e/tcp_position", 3), ("unnamed_model/position", 3), ("unnamed_model/active", 1)]
+        lo, hi = np.array([-0.2, -0.6, 0.02, 0.0]), np.array([0.2, -0.3, 0.3, 0.085])
+    else:
+        t.set("action_lo", [-0.05] * 6 + [0.0]); t.set("action_hi", [0.05] * 6 + [0.085])
+        keys = [("ur5e/joint_configuration", 6), ("unnamed_model/position", 3), ("unnamed_model/active", 1)]
+        lo, hi = np.array([-3.14] * 6 + [0.0]), np.array([3.14] * 6 + [0.085])
     vis = _geom_visuals(comp, active={"switch/button": (0, 1, 0, 1)})  # switch.py:59: green while active
     # scene camera and the wrist camera riding on the flange (robot_push_button.py:51-55,87-96); the flange frame is the
     # frame of the gripper palm geom's body up to the geom's own offset, so the wrist camera is anchored to wrist_3's geom
@@ -428,5 +442,5 @@ def build_push_button(max_steps: int = 100, button_disturbances: bool = False) -
     gw = comp.geom_id["ur5e/w3_col"]  # cylinder at (0, 0.08, 0), quat (1, 1, 0, 0) in wrist_3; flange site at (0, 0.1, 0), quat (-1, 1, 0, 0)
     wp, wq = _in_geom_frame((0, 0.08, 0), (1, 1, 0, 0), (0, 0.1, 0), (-1, 1, 0, 0), (0.0, 0.05, 0.0), (0.0, 0.0, 0.999, 0.04))
     cams["wrist"] = _camera(wp, wq, 42, geom=gw)
-    return TaskBundle("robot_push_button", comp, t, keys, np.array([-3.14] * 6 + [0.0]), np.array([3.14] * 6 + [0.085]), np.float64,
+    return TaskBundle("robot_push_button", comp, t, keys, lo, hi, np.float64,
                       visuals=vis, cameras=cams, image_resolution=96)

@@ -1430,13 +1430,16 @@ void write_obs_reward(const MjsModel* m, const MjsTask* t, MjsEnvState* s, const
       else reward = (-sum / t->n_obj - t->nearest_coef * nearest) * 0.1;
       accomplished = within == t->n_obj;
     } else {  // BUTTON
-      for (int i = 0; i < 6; i++) out->obs[i] = s->qpos[t->arm_qadr + i];
+      // robot_push_button.py:109-113: joint_configuration with ABS_JOINT_ACTION (7 actions), tcp_position with ABS_EEF_ACTION (4)
+      int base = 6;
+      if (t->action_dim == 7) for (int i = 0; i < 6; i++) out->obs[i] = s->qpos[t->arm_qadr + i];
+      else { base = 3; for (int i = 0; i < 3; i++) out->obs[i] = tcp[i]; }
       // switch.py:86-87: button geom xpos + 0.5*size[1] added to all three coordinates
       // (the button geom is geom `touch geom` = the site's own position)
       const double* bp = d->site_xpos + 3 * m->touch_site;
       double quirk = 0.5 * (m->touch_size[0] / 1.01);
-      for (int i = 0; i < 3; i++) out->obs[6 + i] = bp[i] + quirk;
-      out->obs[9] = s->sw_active;
+      for (int i = 0; i < 3; i++) out->obs[base + i] = bp[i] + quirk;
+      out->obs[base + 3] = s->sw_active;
       double df[3];
       sub3(df, tcp, t->button_goal);
       bool goal = s->sw_active && norm3(df) < t->button_goal_radius;  // robot_push_button.py:205-210
@@ -1643,6 +1646,11 @@ void oracle_demo_policy(const MjsModel* m, const MjsTask* t, const MjsEnvState* 
       for (int k = 0; k < 3; k++) { df[k] = goal[k] - tcp[k]; mx = std::max(mx, std::fabs(df[k])); }
       if (mx > lim) for (int k = 0; k < 3; k++) df[k] = df[k] * 0.5 / mx * t->control_dt;
       double tgt[3] = {tcp[0] + df[0], tcp[1] + df[1], tcp[2] + df[2]}, q[6];
+      if (t->action_dim != 7) {  // ABS_EEF_ACTION: the Cartesian target + the closed gripper (robot_push_button.py:289-297)
+        for (int k = 0; k < 3; k++) a[k] = tgt[k];
+        a[3] = 0.0; ok[e] = 1;
+        continue;
+      }
       bool good = tcp_to_joints(t, tgt, s->qpos + t->arm_qadr, q);
       for (int i = 0; i < 6; i++) a[i] = good ? q[i] : s->qpos[t->arm_qadr + i];
       a[6] = 0.0;

@@ -184,17 +184,20 @@ def test_push_autoreset_rollout_across_episode_boundaries_matches_the_oracle():
     env.close()
 
 
-def test_button_f64_scripted_rollout_flags_are_exact_on_1024_envs():
-    """Button Push in f64 at the default tolerance: the scripted demonstrator (robot_push_button.py:231-300) drives 1024
+@pytest.mark.parametrize("action_type,n", [("absolute_joint_action", 1024), ("absolute_eef_action", 256)])
+def test_button_f64_scripted_rollout_flags_are_exact_on_1024_envs(action_type, n):
+    """Both action types of robot_push_button.py:143-157 (joint targets through servoJ / TCP position through servoL).
+    Button Push in f64 at the default tolerance: the scripted demonstrator (robot_push_button.py:231-300) drives 1024
     envs through approach, press, toggle, retreat to the end pose and termination.  Free-running on both sides with the same
     float32 actions: pressed / active / success / terminated / truncated identical at every control step, |dq| <= 1e-4
     throughout.  An env is dropped (and counted) from the step the oracle's touch force comes within 1e-6 N of 5 N or 200 N."""
     import mujoco_sim_b200 as ms
     from mujoco_sim_b200.model.tasks import build_push_button
 
-    n, steps, b = 1024, 100, build_push_button()
+    steps, b = 100, build_push_button(action_type=action_type)
     ora = arm_states(b, n, 9)
-    env = ms.make("robot_push_button", n, precision="f64", autoreset=False)
+    env = ms.make("robot_push_button", n, precision="f64", autoreset=False, action_type=action_type)
+    assert env.action_dim == (7 if action_type == "absolute_joint_action" else 4) and env.obs_keys[0][0] == ("ur5e/joint_configuration" if env.action_dim == 7 else "ur5e/tcp_position")
     env.set_state(copy_states(ora.states, n), forward=True)
     ok = np.ones(n, bool); alive = np.ones(n, bool)
     npress = ntoggle = nsucc = nterm = ntrunc = nexcl = 0
@@ -204,9 +207,14 @@ def test_button_f64_scripted_rollout_flags_are_exact_on_1024_envs():
     for k in range(steps):
         a, _ = ora.demo_policy()
         a = a.astype(np.float32)
+        if k % 10 == 0:  # the device demonstrator on the same states (mjs_demo_policy)
+            ad, _ = env.demonstration_actions()
+            assert np.abs(ad.cpu().numpy() - a)[ok & alive].max() < 1e-5
         (obs_o, rew_o, _, fl_o), touch = ora.step_touch(a.astype(np.float64))
-        env.step(torch.from_numpy(a).cuda())
+        obs_d, *_ = env.step(torch.from_numpy(a).cuda())
         q, v, st = _qv(env, 6, 6)
+        flat = torch.cat([obs_d[key] for key, _ in env.obs_keys], 1).cpu().numpy()
+        assert np.abs(flat - obs_o)[ok & alive].max() < 1e-4
         close = (np.minimum(np.abs(touch - lo), np.abs(touch - hi)).min(1) < 1e-6)
         nexcl += int((ok & alive & close).sum())
         ok &= ~close
@@ -225,7 +233,7 @@ def test_button_f64_scripted_rollout_flags_are_exact_on_1024_envs():
         alive &= ~fl_o[:, 3].astype(bool)
         if not alive.any():
             break
-    print("button f64 scripted rollout:", n, "envs,", k + 1, "steps; pressed env-steps", npress, "toggles", ntoggle, "successes", nsucc, "terminated", nterm,
+    print("button f64 scripted rollout", action_type, ":", n, "envs,", k + 1, "steps; pressed env-steps", npress, "toggles", ntoggle, "successes", nsucc, "terminated", nterm,
           "truncated", ntrunc, "threshold exclusions", nexcl, "max|dq| free-running", worst_q)
     assert npress > n // 2 and ntoggle > n // 2 and nterm > n // 2
     assert nexcl <= n // 100

@@ -114,3 +114,39 @@ def test_planar_push_reward_and_flags_follow_the_task_definition():
         done = (d_t < 0.05).all(1)
         np.testing.assert_array_equal(fl[:, 0].astype(bool), done)
         np.testing.assert_allclose(disc, 1.0 - done)
+
+
+def test_button_push_eef_action_variant_follows_the_joint_variant():
+    """robot_push_button.py:143-157: ABS_EEF_ACTION sends the TCP position through servoL (analytic IK, closest solution),
+    ABS_JOINT_ACTION the joint targets through servoJ.  The scripted demonstrator (:231-300) computes a Cartesian target and only
+    converts it to joints for the joint action type with the same IK, so both variants must trace the same motion; the EEF
+    variant observes tcp_position instead of joint_configuration (:109-113)."""
+    from tests.helpers import arm_states
+
+    n = 8
+    bj, be = T.build_push_button(), T.build_push_button(action_type=T.ABS_EEF_ACTION)
+    assert be.task.action_dim == 4 and be.task.obs_dim == 7 and [k for k, _ in be.obs_keys] == ["ur5e/tcp_position", "unnamed_model/position", "unnamed_model/active"]
+    oj, oe = arm_states(bj, n, 21), arm_states(be, n, 21)
+    succ = 0
+    for k in range(100):
+        aj, okj = oj.demo_policy(); ae, oke = oe.demo_policy()
+        assert ae.shape == (n, 4) and oke.all() and (ae[:, 3] == 0).all()
+        obs_j, rew_j, _, fl_j = oj.step(aj); obs_e, rew_e, _, fl_e = oe.step(ae)
+        np.testing.assert_allclose(oe.field("qpos", 6), oj.field("qpos", 6), atol=1e-9)
+        np.testing.assert_array_equal(fl_e, fl_j)
+        np.testing.assert_allclose(obs_e[:, 3:7], obs_j[:, 6:10], atol=1e-9)          # switch position + active
+        tcp = np.array([ur_fk_tcp(be, q) for q in oe.field("qpos", 6)])
+        # tcp_position observable = the MJCF site; the DH chain of the analytic IK differs from the MJCF by ~1 mm
+        # (the reference's own FK check uses atol 1e-2: test/test_ur_frame_matches_real.py)
+        np.testing.assert_allclose(obs_e[:, :3], tcp, atol=2e-3)
+        succ += int(fl_e[:, 2].sum())
+        if fl_e[:, 3].all():
+            break
+    assert succ >= n // 2
+
+
+def ur_fk_tcp(bundle, q):
+    """analytic FK of the flange (oracle.ur_fk) + the TCP offset along the tool axis (robot.py:126-136)"""
+    T06 = ur_fk(np.array([bundle.task.ik_dh[k] for k in range(6)]), np.asarray(q, float))
+    off = np.array([bundle.task.tcp_offset[k] for k in range(3)])
+    return T06[:3, 3] + T06[:3, :3] @ off

@@ -80,6 +80,7 @@ def test_visual_observation_type_returns_the_cameras_and_the_enabled_state_keys(
     es = ms.make(task, n, seed=11)
     ov, _ = ev.reset(); os_, _ = es.reset()
     keep, cams = _VISUAL[task]
+    keep = ev._visual_keep
     assert list(ov) == keep + [k for k, _ in cams]
     for _ in range(3):
         ov, rv, tv, trv, iv = ev.step(None); os_, rs, ts, trs, is_ = es.step(None)
