@@ -18,8 +18,10 @@ ArmSim* arm_create(const MjsModel& m, const MjsTask& t, int N, unsigned long lon
   a->nobj = a->mf.nobj;
   if (a->mf.npair + ARM_NLINK > 32) { mjs_set_error("arm engine: npair + 6 limit lanes exceed one warp"); delete a; return nullptr; }
   if (a->nobj == 0) layout_sizes<0>(a->SD, a->SI);
+  else if (a->nobj == 1) layout_sizes<1>(a->SD, a->SI);
+  else if (a->nobj == 2) layout_sizes<2>(a->SD, a->SI);
   else if (a->nobj == 3) layout_sizes<3>(a->SD, a->SI);
-  else { mjs_set_error("arm engine: built for 0 or 3 props, got %d", a->nobj); delete a; return nullptr; }
+  else { mjs_set_error("arm engine: built for 0 to 3 props, got %d", a->nobj); delete a; return nullptr; }
   if (cudaMalloc(&a->sd, sizeof(double) * (size_t)a->SD * N) != cudaSuccess || cudaMalloc(&a->si, sizeof(int) * (size_t)a->SI * N) != cudaSuccess) {
     mjs_set_error("arm engine: cudaMalloc failed"); delete a; return nullptr;
   }
@@ -246,8 +248,8 @@ int arm_set_state(ArmSim* a, const MjsEnvState* h, int first, int count, int for
   std::vector<double> sd((size_t)a->SD * count);
   std::vector<int> si((size_t)a->SI * count);
   for (int i = 0; i < count; i++) {
-    if (a->nobj == 0) pack<0>(h[i], sd.data() + (size_t)i * a->SD, si.data() + (size_t)i * a->SI);
-    else pack<3>(h[i], sd.data() + (size_t)i * a->SD, si.data() + (size_t)i * a->SI);
+    double* d = sd.data() + (size_t)i * a->SD; int* q = si.data() + (size_t)i * a->SI;
+    switch (a->nobj) { case 0: pack<0>(h[i], d, q); break; case 1: pack<1>(h[i], d, q); break; case 2: pack<2>(h[i], d, q); break; default: pack<3>(h[i], d, q); }
   }
   MJS_CUDA_CHECK(cudaMemcpy(a->sd + (size_t)first * a->SD, sd.data(), sd.size() * sizeof(double), cudaMemcpyHostToDevice));
   MJS_CUDA_CHECK(cudaMemcpy(a->si + (size_t)first * a->SI, si.data(), si.size() * sizeof(int), cudaMemcpyHostToDevice));
@@ -265,8 +267,8 @@ int arm_get_state(ArmSim* a, MjsEnvState* h, int first, int count) {
   MJS_CUDA_CHECK(cudaMemcpy(sd.data(), a->sd + (size_t)first * a->SD, sd.size() * sizeof(double), cudaMemcpyDeviceToHost));
   MJS_CUDA_CHECK(cudaMemcpy(si.data(), a->si + (size_t)first * a->SI, si.size() * sizeof(int), cudaMemcpyDeviceToHost));
   for (int i = 0; i < count; i++) {
-    if (a->nobj == 0) unpack<0>(h[i], sd.data() + (size_t)i * a->SD, si.data() + (size_t)i * a->SI);
-    else unpack<3>(h[i], sd.data() + (size_t)i * a->SD, si.data() + (size_t)i * a->SI);
+    const double* d = sd.data() + (size_t)i * a->SD; const int* q = si.data() + (size_t)i * a->SI;
+    switch (a->nobj) { case 0: unpack<0>(h[i], d, q); break; case 1: unpack<1>(h[i], d, q); break; case 2: unpack<2>(h[i], d, q); break; default: unpack<3>(h[i], d, q); }
   }
   return 0;
 }

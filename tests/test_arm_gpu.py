@@ -272,3 +272,45 @@ def test_step_host_matches_device_step():
         np.testing.assert_array_equal(obs, e2._obs.cpu().numpy())
         np.testing.assert_array_equal(rew, e2._reward.cpu().numpy())
     e1.close(); e2.close()
+
+
+@pytest.mark.parametrize("n_objects", [1, 2])
+def test_push_with_fewer_props_matches_the_oracle(n_objects):
+    """RobotPushConfig.n_objects (robot_planar_push.py:61) = 1 and 2: single control steps from identical states (pusher driven at a
+    prop on every other step) at 1e-4, reward / flags / observation equal; then a device reset + 3 device-drawn steps must be
+    bit-identical between two differently sized batches (Philox keyed by the global env id)."""
+    import mujoco_sim_b200 as ms
+    from mujoco_sim_b200.model.tasks import RobotPushConfig, build_planar_push
+
+    n = 128
+    b = build_planar_push(RobotPushConfig(n_objects=n_objects))
+    assert b.task.obs_dim == 5 + 2 * n_objects and b.model.nv == 6 + 6 * n_objects
+    ora = push_states(b, n, 3)
+    env = _env("robot_planar_push", n, "f64", b)
+    rng = np.random.RandomState(4)
+    nq, nv = 6 + 7 * n_objects, 6 + 6 * n_objects
+    worst = 0.0; moved = 0
+    for k in range(6):
+        env.set_state(copy_states(ora.states, n), forward=False)
+        q0 = ora.field("qpos", nq)
+        a = _push_actions(ora, rng, n, k)
+        obs_o, rew_o, _, fl_o = ora.step(a.astype(np.float64))
+        obs, rew, *_ = env.step(torch.from_numpy(a).cuda())
+        q, v, _ = _qv(env, nq, nv)
+        worst = max(worst, np.abs(q - ora.field("qpos", nq)).max())
+        moved += int((np.abs(ora.field("qpos", nq)[:, 6:] - q0[:, 6:]).max(1) > 1e-5).sum())
+        flat = torch.cat([obs[key] for key, _ in env.obs_keys], 1).cpu().numpy()
+        assert np.abs(flat - obs_o).max() < 1e-4 and np.abs(rew.cpu().numpy() - rew_o).max() < 1e-4
+        np.testing.assert_array_equal(env._flags.cpu().numpy(), fl_o)
+    print(f"push with {n_objects} prop(s): max|dq| {worst:.2e} over {6 * n} env-steps, {moved} with moving props")
+    assert worst < TOL_CONTACT_STEP and moved > 20
+    env.close()
+    big = ms.make("robot_planar_push", 96, seed=7, config=RobotPushConfig(n_objects=n_objects))
+    small = ms.make("robot_planar_push", 32, seed=7, env_offset=64, config=RobotPushConfig(n_objects=n_objects))
+    big.reset(); small.reset()
+    for _ in range(3):
+        ob, rb, *_ = big.step(None); os_, rs, *_ = small.step(None)
+    for key, _ in big.obs_keys:
+        assert torch.equal(ob[key][64:], os_[key])
+    assert torch.equal(rb[64:], rs)
+    big.close(); small.close()
