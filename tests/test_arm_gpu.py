@@ -314,3 +314,11 @@ def test_push_with_fewer_props_matches_the_oracle(n_objects):
         assert torch.equal(ob[key][64:], os_[key])
     assert torch.equal(rb[64:], rs)
     big.close(); small.close()
+    # the FP32-dynamics instantiation of the same prop count: runs, stays finite, tracks the f64 path on quiet steps
+    mx = ms.make("robot_planar_push", 64, seed=7, precision="mixed", config=RobotPushConfig(n_objects=n_objects))
+    fx = ms.make("robot_planar_push", 64, seed=7, config=RobotPushConfig(n_objects=n_objects))
+    mx.reset(); fx.reset()
+    om, *_ = mx.step(None); of, *_ = fx.step(None)
+    d = (om["block_positions"] - of["block_positions"]).abs().max(1).values
+    assert torch.isfinite(om["block_positions"]).all() and float(d.median()) < 1e-5 and int(mx.status().abs().sum()) == 0
+    mx.close(); fx.close()
