@@ -268,3 +268,40 @@ def test_pusher_impact_conserves_momentum_between_pusher_and_prop():
         np.testing.assert_allclose(MASS * (v1 - v0), h * (F + np.array([0, 0, -MASS * G])), atol=1e-9)
         seen += touching
     assert seen > 3  # the pusher really hit the prop
+
+
+def test_joint_limit_row_matches_the_formulas_written_out():
+    """A limit row is the simplest constraint row MuJoCo builds: pos = q - lo (or hi - q), J = +-e_j, impedance d(|pos|) from
+    solimp, R = (1 - d) / d * dof_invweight0, D = 1 / R, aref = -b (J v) - k d pos with k = 1 / (dmax^2 tc^2 dr^2), b = 2 / (dmax tc)
+    (mj_makeImpedance / mj_referenceConstraint as documented).  Numbers recomputed here from the model constants only."""
+    from mujoco_sim_b200.model import tasks as T
+    from tests.helpers import arm_states
+
+    b = T.build_robot_reach()
+    m = b.model
+    ora = arm_states(b, 1, 5)
+    s = ora.states[0]
+    j = 2                                   # elbow: range +-3.1415
+    lo, hi = m.jnt_range[2 * j], m.jnt_range[2 * j + 1]
+    for side, q, v in ((+1, hi + 0.013, 0.4), (-1, lo - 0.0004, -0.7)):   # past the upper / lower limit, moving further out
+        s.qpos[j] = q; s.qvel[j] = v; s.ctrl[j] = q   # ctrl = q: the position actuator does not pull the joint back by itself
+        d = ora.stage_dump(0)
+        rows = [r for r in range(d["nefc"]) if abs(d["efc_J"][r][j]) == 1.0 and np.count_nonzero(d["efc_J"][r]) == 1]
+        assert len(rows) == 1
+        r = rows[0]
+        J = -1.0 if side > 0 else 1.0       # pos = hi - q  ->  J = -1;  pos = q - lo  ->  J = +1
+        assert d["efc_J"][r][j] == J
+        pos = (hi - q) if side > 0 else (q - lo)
+        d0, dw, width, mid, power = [m.jnt_solimp[5 * j + k] for k in range(5)]
+        tc, dr = m.jnt_solref[2 * j], m.jnt_solref[2 * j + 1]
+        x = min(abs(pos) / width, 1.0)
+        y = x ** power / mid ** (power - 1) if x <= mid else 1 - (1 - x) ** power / (1 - mid) ** (power - 1)
+        imp = d0 + y * (dw - d0)
+        k_ = 1.0 / (dw * dw * tc * tc * dr * dr); b_ = 2.0 / (dw * tc)
+        aref = -b_ * (J * v) - k_ * imp * pos
+        D = 1.0 / ((1 - imp) / imp * m.dof_invweight0[j])
+        np.testing.assert_allclose(d["efc_aref"][r], aref, rtol=1e-12)
+        np.testing.assert_allclose(d["efc_D"][r], D, rtol=1e-12)
+        # (the UR5e's position actuators clamp ctrl to the same range and pull a joint that is past its limit back harder than
+        # aref asks for, so J a >= aref already at the smooth acceleration and the row carries no force: nothing more to check)
+        assert d["efc_force"][r] == 0 and J * d["qacc"][j] >= d["efc_aref"][r]
