@@ -40,11 +40,7 @@ __device__ __forceinline__ const ArmModel<real>& cmodel() { return *reinterpret_
 // records): a constant-cache load with a different address per lane is replayed once per address, an L1-cached global
 // load is one coalesced request.  Measured +3.5 % (f64) / +12 % (FP32) on Planar Push.  Uniform scalars stay in c[].
 __device__ __align__(16) unsigned char g_arm_model[sizeof(ArmModel<double>)];
-#ifdef ARM_MODEL_CONST_ONLY
-#define GM() (cmodel<real>())
-#else
 #define GM() (*reinterpret_cast<const ArmModel<real>*>(g_arm_model))
-#endif
 
 #ifdef MJS_STAGE_CLOCKS_REPEAT
 #define MJS_NCLK 14  // + second (instruction-cache-hot) runs of dynamics and collision
@@ -107,12 +103,6 @@ __device__ __forceinline__ int shfl(int v, int src) { return __shfl_sync(FULLMAS
 __device__ __forceinline__ float shfl_up(float v, int d) { return __shfl_up_sync(FULLMASK, v, d); }
 __device__ __forceinline__ float shfl_down(float v, int d) { return __shfl_down_sync(FULLMASK, v, d); }
 __device__ __forceinline__ float shfl_xor(float v, int m) { return __shfl_xor_sync(FULLMASK, v, m); }
-#ifdef MJS_STOCK_SHFL
-__device__ __forceinline__ double shfl(double v, int src) { return __shfl_sync(FULLMASK, v, src); }
-__device__ __forceinline__ double shfl_up(double v, int d) { return __shfl_up_sync(FULLMASK, v, d); }
-__device__ __forceinline__ double shfl_down(double v, int d) { return __shfl_down_sync(FULLMASK, v, d); }
-__device__ __forceinline__ double shfl_xor(double v, int m) { return __shfl_xor_sync(FULLMASK, v, m); }
-#else
 #define MJS_SHFL64(NAME, OP)                                                          \
   __device__ __forceinline__ double NAME(double v, int a) {                           \
     int lo = OP(FULLMASK, __double2loint(v), a), hi = OP(FULLMASK, __double2hiint(v), a); \
@@ -123,7 +113,6 @@ MJS_SHFL64(shfl_up, __shfl_up_sync)
 MJS_SHFL64(shfl_down, __shfl_down_sync)
 MJS_SHFL64(shfl_xor, __shfl_xor_sync)
 #undef MJS_SHFL64
-#endif
 template <typename T>
 __device__ __forceinline__ T warp_sum(T v) {
 #pragma unroll
@@ -133,9 +122,6 @@ __device__ __forceinline__ T warp_sum(T v) {
 
 template <typename real> __device__ __forceinline__ void sincos_r(real x, real* s, real* c);
 template <> __device__ __forceinline__ void sincos_r<float>(float x, float* s, float* c) { sincosf(x, s, c); }
-#ifdef MJS_STOCK_SINCOS
-template <> __device__ __forceinline__ void sincos_r<double>(double x, double* s, double* c) { sincos(x, s, c); }
-#else
 // sin / cos of a joint half-angle or a quaternion increment in ~35 instructions instead of the ~160 of sincos(): two-constant
 // Cody-Waite reduction by pi/2 (exact enough for |x| < 1e5; the arguments here are bounded by the joint ranges) and the
 // fdlibm kernel polynomials on [-pi/4, pi/4].  Max error against libm over [-7, 7]: 1.1e-16 (tools/check_sincos.py).
@@ -154,7 +140,6 @@ template <> __device__ __forceinline__ void sincos_r<double>(double x, double* s
   *s = (k & 2) ? -ss : ss;
   *c = ((k + 1) & 2) ? -cc : cc;
 }
-#endif
 template <typename real> __device__ __forceinline__ real rsqrt_r(real x);
 template <> __device__ __forceinline__ float rsqrt_r<float>(float x) { return rsqrtf(x); }
 // rsqrt(double): MUFU.RSQ64H seed + Newton steps (~1 ulp), a quarter of the instructions of 1.0 / sqrt(x)
@@ -343,11 +328,7 @@ struct ArmEngine {
   // that wait for the slowest member of their group lose less when the group is smaller, at the price of
   // sharing instruction fetches among fewer warps.
   static constexpr int SYNC_GROUP = sizeof(real) == 8 ? ARM_SYNC_GROUP_F64 : ARM_SYNC_GROUP_F32;
-#ifdef ARM_GROUP_SMSP  // experiment: groups follow the warp -> scheduler mapping (warp % 4) instead of warp / SYNC_GROUP
-  __device__ static __forceinline__ int group_id() { return 1 + (((threadIdx.x >> 5) & 3) * ARM_GROUP_SMSP) / 4; }
-#else
   __device__ static __forceinline__ int group_id() { return 1 + (threadIdx.x >> 5) / SYNC_GROUP; }
-#endif
   __device__ static __forceinline__ void group_sync() {
     int id = group_id();
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(SYNC_GROUP * 32) : "memory");
@@ -472,72 +453,6 @@ struct ArmEngine {
   // qfrc_passive - qfrc_bias + qfrc_actuator for every dof.  Gravity compensation
   // (robot.py:81-82) is folded into the RNE gravity term: each body feels
   // (1 - gravcomp) * m * g.  Returns the actuator "force is clamped" flag (lane j).
-#ifdef MJS_DYNAMICS_SCAN
-  __device__ static bool dynamics(const AM& A, WM& W, int lane) {
-    real Sj[6] = {0, 0, 0, 0, 0, 0}, qd = 0;
-    if (lane < ARM_NLINK) {
-#pragma unroll
-      for (int k = 0; k < 6; k++) Sj[k] = W.S[lane][k];
-      qd = (real)W.qvel[lane];
-    }
-    // inclusive prefix scans along the chain: spatial velocity, then bias acceleration
-    real v[6], acc[6];
-#pragma unroll
-    for (int k = 0; k < 6; k++) v[k] = Sj[k] * qd;
-#pragma unroll ROLL
-    for (int o = 1; o < 8; o <<= 1) {
-#pragma unroll
-      for (int k = 0; k < 6; k++) { real t = shfl_up(v[k], o); if (lane >= o) v[k] += t; }
-    }
-    {
-      real vprev[6], sd[6];
-#pragma unroll
-      for (int k = 0; k < 6; k++) vprev[k] = v[k] - Sj[k] * qd;
-      cross_motion(sd, vprev, Sj);
-#pragma unroll
-      for (int k = 0; k < 6; k++) acc[k] = sd[k] * qd;
-    }
-#pragma unroll ROLL
-    for (int o = 1; o < 8; o <<= 1) {
-#pragma unroll
-      for (int k = 0; k < 6; k++) { real t = shfl_up(acc[k], o); if (lane >= o) acc[k] += t; }
-    }
-    // inertial bodies (lanes < nab): spatial inertia about the origin + body force
-    real I[10], f[6];
-#pragma unroll
-    for (int k = 0; k < 10; k++) I[k] = 0;
-#pragma unroll
-    for (int k = 0; k < 6; k++) f[k] = 0;
-    int mylink = lane < A.nab ? GM().ab_link[lane] : 0;
-    real vb[6], ab[6];
-#pragma unroll
-    for (int k = 0; k < 6; k++) { vb[k] = shfl(v[k], mylink); ab[k] = shfl(acc[k], mylink); }
-    if (lane < A.nab) body_inertia_force(A, W, lane, mylink, vb, ab, I, f);
-    // fold the fixed attachments (lanes 6,7) into their link lane
-#pragma unroll ROLL
-    for (int a = ARM_NLINK; a < ARM_MAXAB; a++) {
-      int al = shfl(mylink, a);
-      bool take = (a < A.nab) && (lane == al);
-#pragma unroll
-      for (int k = 0; k < 10; k++) { real t = shfl(I[k], a); if (take) I[k] += t; }
-#pragma unroll
-      for (int k = 0; k < 6; k++) { real t = shfl(f[k], a); if (take) f[k] += t; }
-    }
-    if (lane >= ARM_NLINK) {
-#pragma unroll
-      for (int k = 0; k < 10; k++) I[k] = 0;
-#pragma unroll
-      for (int k = 0; k < 6; k++) f[k] = 0;
-    }
-    // suffix scans: composite inertia and accumulated force of the sub-chain
-#pragma unroll ROLL
-    for (int o = 1; o < 8; o <<= 1) {
-#pragma unroll
-      for (int k = 0; k < 10; k++) { real t = shfl_down(I[k], o); if (lane + o < ARM_NLINK) I[k] += t; }
-#pragma unroll
-      for (int k = 0; k < 6; k++) { real t = shfl_down(f[k], o); if (lane + o < ARM_NLINK) f[k] += t; }
-    }
-#else
   // Every inertial-body lane (6 links + <= 2 fixed attachments) walks the chain up to its own link in registers -- motion axes and
   // joint rates come from shared memory -- instead of prefix scans through shuffles; the bodies' spatial inertias and forces go
   // through a shared-memory scratch (the contact Jacobian block, free until make_rows) and every link lane sums its sub-chain.
@@ -584,7 +499,6 @@ struct ArmEngine {
         }
       }
     }
-#endif
     bool clamped = false;
     if (lane < ARM_NLINK) {
       real tau = 0;
@@ -976,41 +890,6 @@ struct ArmEngine {
           int slot = GM().geom_slot[g];
           real sg = side == 0 ? (real)-1 : (real)1;
           int blk = -1, cols = 0;
-#ifdef MJS_ROWS_V1
-          if (slot >= SLOT_LINK0 && slot < SLOT_LINK0 + ARM_NLINK) {
-            blk = 0; cols = slot - SLOT_LINK0 + 1;
-            for (int j = 0; j < cols; j++) {
-              real Sa[3] = {W.S[j][0], W.S[j][1], W.S[j][2]}, jp[3];
-              cross3(jp, Sa, pos);
-              jp[0] += W.S[j][3]; jp[1] += W.S[j][4]; jp[2] += W.S[j][5];
-              for (int k = 0; k < nrow; k++) {
-                real val = k < 3 ? dot3(fr + 3 * k, jp) : dot3(fr, Sa);
-                W.cJ[(side * 4 + k) * 6 + j][c] = sg * val;
-                u[k] += sg * val * W.qv[j];
-              }
-            }
-          } else if (slot >= SLOT_OBJ0 && slot < SLOT_OBJ0 + ARM_MAXOBJ) {
-            int ob = slot - SLOT_OBJ0;
-            blk = 1 + ob; cols = 6;
-            const real* R = W.xmat[slot];
-            real r[3] = {pos[0] - W.xpos[slot][0], pos[1] - W.xpos[slot][1], pos[2] - W.xpos[slot][2]};
-            int b0 = ARM_NLINK + 6 * ob;
-            for (int k = 0; k < nrow; k++) {
-              for (int j = 0; j < 3; j++) {
-                real val = k < 3 ? fr[3 * k + j] : (real)0;
-                W.cJ[(side * 4 + k) * 6 + j][c] = sg * val;
-                u[k] += sg * val * W.qv[b0 + j];
-              }
-              for (int j = 0; j < 3; j++) {
-                real Ra[3] = {R[j], R[3 + j], R[6 + j]}, jp[3];
-                cross3(jp, Ra, r);
-                real val = k < 3 ? dot3(fr + 3 * k, jp) : dot3(fr, Ra);
-                W.cJ[(side * 4 + k) * 6 + 3 + j][c] = sg * val;
-                u[k] += sg * val * W.qv[b0 + 3 + j];
-              }
-            }
-          }
-#else
           // Row loops are unrolled with `k < nrow` guards so that fr[] and u[] are indexed statically (registers, not the
           // thread's stack frame), and the lever-arm cross product of a column is formed once, not once per row.
           if (slot >= SLOT_LINK0 && slot < SLOT_LINK0 + ARM_NLINK) {
@@ -1061,7 +940,6 @@ struct ArmEngine {
               }
             }
           }
-#endif
           W.cblk[side][c] = blk; W.ccols[side][c] = cols;
         }
         C.mu[0] = GM().pair_mu[p][0]; C.mu[1] = GM().pair_mu[p][0]; C.mu[2] = GM().pair_mu[p][1];
@@ -1209,12 +1087,7 @@ struct ArmEngine {
   // arm shares no contact with a prop either (coup == 0, the common case) the
   // Hessian is block-diagonal and the arm block rides in the same 6 column steps
   // and the same 6 + 6 substitution steps as the props: half the serial chain.
-#ifdef MJS_SHARED_CHOL
-  // one copy, called by the Newton loop and by the integrator (second call runs hot in the instruction cache)
-  __device__ static __noinline__ real block_direction(WM& W, int lane, real b) {
-#else
   __device__ static __forceinline__ real block_direction(WM& W, int lane, real b) {
-#endif
     const bool isarm = lane < ARM_NLINK, isobj = lane >= ARM_NLINK && lane < NV;
     const int myc = isarm ? lane : (lane - ARM_NLINK) % 6;
     const int base = isarm ? 6 * NOBJ : ((lane - ARM_NLINK) / 6) * 6;
@@ -1223,7 +1096,6 @@ struct ArmEngine {
     const bool indep = coup == 0;                   // warp-uniform
     const bool isblk = isobj || (isarm && indep);   // lanes of the parallel diagonal-block pass
     const int lane0 = isarm ? 0 : ARM_NLINK + base; // lane that owns column 0 of this lane's block
-#ifndef MJS_CHOL_COOPERATIVE
     if (indep) {
       // block-diagonal Hessian (the common case): every lane solves its own 6x6 block in registers
       real rhs[6];
@@ -1243,7 +1115,6 @@ struct ArmEngine {
       }
       return x;
     }
-#endif
     real rdiag = 1;
     // diagonal blocks (props, and the arm when it is uncoupled)
 #pragma unroll CHOLU
@@ -1433,37 +1304,6 @@ struct ArmEngine {
       if (!done) {
         nit++;
         // ---- Hessian rows H = M + sum_c Jc^T W_c Jc (solver ordering)
-#ifdef MJS_HESS_V1
-        if (isdof) {
-          for (int j = 0; j < NV; j++) W.H[si][j] = 0;
-          if (lane < ARM_NLINK) {
-  #pragma unroll
-            for (int j = 0; j < ARM_NLINK; j++) W.H[si][sidx(j)] = W.Marm[lane][j];
-          } else W.H[si][si] = mdiag;
-          int n = W.bcount[myblk];
-          for (int r = 0; r < n; r++) {
-            int e = W.blist[myblk][r], c = e & 0xff, side = e >> 8;
-            real jm[4], z[4];
-  #pragma unroll
-            for (int k = 0; k < 4; k++) jm[k] = W.cJ[(side * 4 + k) * 6 + d][c];
-            z[0] = W.cW[0][c] * jm[0] + W.cW[1][c] * jm[1] + W.cW[2][c] * jm[2] + W.cW[3][c] * jm[3];
-  #pragma unroll
-            for (int k = 0; k < 3; k++) z[1 + k] = W.cW[1 + k][c] * jm[0] + W.cW[4 + k][c] * jm[1 + k];
-  #pragma unroll ROLL
-            for (int s2 = 0; s2 < 2; s2++) {
-              int blk2 = W.cblk[s2][c];
-              if (blk2 < 0) continue;
-              int b2 = blk_base(blk2), cols2 = W.ccols[s2][c];
-              for (int j = 0; j < cols2; j++) {
-                real t = 0;
-  #pragma unroll
-                for (int k = 0; k < 4; k++) t += z[k] * W.cJ[(s2 * 4 + k) * 6 + j][c];
-                W.H[si][sidx(b2 + j)] += t;
-              }
-            }
-          }
-        }
-#else
         // The row's own diagonal block accumulates in registers and is stored once; entries outside the block exist only
         // when a contact couples two blocks (coup / objcoup), and only then is the row cleared and updated in shared memory
         // (block_direction never reads an off-block entry of an uncoupled Hessian).
@@ -1512,7 +1352,6 @@ struct ArmEngine {
 #pragma unroll
           for (int j = 0; j < 6; j++) W.H[si][ownbase + j] = hown[j];
         }
-#endif
         __syncwarp();
       }
       STAGE_CLK(W, 5, tclk);
@@ -1623,28 +1462,6 @@ struct ArmEngine {
   __device__ static void integrate(const AM& A, WM& W, int lane, bool clamped, double& time) {
     const real h = A.timestep;
     real qacc = 0;
-#ifdef MJS_SHARED_CHOL
-    // The integrator's system is block-diagonal (arm: M + h kv; props: their constant inertia): write it into the
-    // (now free) Hessian scratch in solver order and reuse the Newton direction routine with no coupling.
-    if (lane < NV) {
-      const bool isarm = lane < ARM_NLINK;
-      const int myc = isarm ? lane : (lane - ARM_NLINK) % 6;
-      const int base = isarm ? 6 * NOBJ : ((lane - ARM_NLINK) / 6) * 6;
-      if (isarm) {
-        real dv = (A.integrator == MJS_INT_IMPLICITFAST && !clamped) ? (real)GM().kv[lane] : (real)0;
-#pragma unroll
-        for (int j = 0; j < ARM_NLINK; j++) W.H[base + myc][base + j] = W.Marm[lane][j] + (j == lane ? h * dv : (real)0);
-      } else {
-        int k = (lane - ARM_NLINK) / 6;
-        real md = myc < 3 ? GM().obj_mass[k] : GM().obj_I[k][myc - 3];
-#pragma unroll
-        for (int j = 0; j < 6; j++) W.H[base + myc][base + j] = j == myc ? md : (real)0;
-      }
-    }
-    if (lane == 0) W.coup = 0;
-    __syncwarp();
-    qacc = block_direction(W, lane, lane < NV ? W.fsm[lane] + W.fcon[lane] : (real)0);
-#else
     if (lane < ARM_NLINK) {
       real dv = (A.integrator == MJS_INT_IMPLICITFAST && !clamped) ? (real)GM().kv[lane] : (real)0;
       // 6x6 system in the (now free) Hessian scratch, lanes 0..5 = rows
@@ -1652,7 +1469,6 @@ struct ArmEngine {
       for (int j = 0; j < ARM_NLINK; j++) W.H[lane][j] = W.Marm[lane][j] + (j == lane ? h * dv : (real)0);
     }
     __syncwarp();
-#ifndef MJS_CHOL_COOPERATIVE
     {
       real rhs[6];
       const real bi = lane < NV ? W.fsm[lane] + W.fcon[lane] : (real)0;
@@ -1673,41 +1489,6 @@ struct ArmEngine {
         qacc = bi / (d < 3 ? GM().obj_mass[k] : GM().obj_I[k][d - 3]);
       }
     }
-#else
-    real rdiag = 1;
-#pragma unroll
-    for (int k = 0; k < ARM_NLINK; k++) {
-      real s = 0;
-      if (lane < ARM_NLINK && lane >= k) {
-        s = W.H[lane][k];
-        for (int j = 0; j < k; j++) s -= W.H[lane][j] * W.H[k][j];
-      }
-      real dk = shfl(s, k);
-      real rd = rsqrt_r<real>(dk);
-      if (lane < ARM_NLINK) {
-        if (lane == k) { W.H[lane][k] = dk * rd; rdiag = rd; }
-        else if (lane > k) W.H[lane][k] = s * rd;
-      }
-      __syncwarp();
-    }
-    real b = lane < NV ? W.fsm[lane] + W.fcon[lane] : (real)0;
-#pragma unroll
-    for (int k = 0; k < ARM_NLINK; k++) {
-      real yk = shfl(b * rdiag, k);
-      if (lane < ARM_NLINK) { if (lane == k) b = yk; else if (lane > k) b -= W.H[lane][k] * yk; }
-    }
-#pragma unroll
-    for (int k = ARM_NLINK - 1; k >= 0; k--) {
-      real xk = shfl(b * rdiag, k);
-      if (lane < ARM_NLINK) { if (lane == k) b = xk; else if (lane < k) b -= W.H[k][lane] * xk; }
-    }
-    if (lane < ARM_NLINK) qacc = b;
-    else if (lane < NV) {
-      int k = (lane - ARM_NLINK) / 6, d = (lane - ARM_NLINK) % 6;
-      qacc = b / (d < 3 ? GM().obj_mass[k] : GM().obj_I[k][d - 3]);
-    }
-#endif
-#endif
     // mj_advance in double
     if (lane < NV) W.qvel[lane] += (double)h * (double)qacc;
     __syncwarp();
@@ -1779,40 +1560,6 @@ struct ArmEngine {
   // composer loop's "step2 then step1" order is the same sequence seen from the
   // state's point of view (ArmTask::control_step).  Deliberately NOT inlined:
   // one copy of the heavy code keeps the instruction footprint inside the i-cache.
-#ifdef MJS_SUBSTEP_ONE_PIECE
-  __device__ static __noinline__ SubRes substep(WM* Wp, int lane, real a_i, double time, int do_integrate, SepAxis<real> sep = SepAxis<real>MJS_SEP_ZERO) {
-    const AM& A = cmodel<real>();
-    WM& W = *Wp;
-    ConReg C;
-    if (!(do_integrate & 2)) stage_sync(W, 1);
-    long long tclk = clock64(); (void)tclk;
-    kinematics(A, W, lane);
-    STAGE_CLK(W, 0, tclk);
-    stage_sync(W, 3);
-    bool clamped = dynamics(A, W, lane);
-    STAGE_CLK(W, 1, tclk);
-    stage_sync(W, 3);
-    bool cvx;
-    collide(A, W, lane, sep, cvx);
-    if (__any_sync(FULLMASK, cvx)) sep = convex_fixup(&W, lane, cvx, sep);  // rare: pairs without an analytic routine (cap contacts)
-    STAGE_CLK(W, 2, tclk);
-    stage_sync(W, 3);
-    make_rows(A, W, lane, C);
-    STAGE_CLK(W, 3, tclk);
-    stage_sync(W, 2);
-    SubRes r;
-    r.niter = solve(A, W, lane, C, a_i);
-    tclk = clock64();
-    r.touch = touch_force(A, W, lane, C);
-    stage_sync(W, 3);
-    if (do_integrate & 1) integrate(A, W, lane, clamped, time);
-    STAGE_CLK(W, 9, tclk);
-    r.a_i = a_i;
-    r.time = time;
-    r.sep = sep;
-    return r;
-  }
-#else
   // The substep is two non-inlined halves -- mj_step1 up to the narrowphase, then rows / solve / integrate -- with the rare
   // general-convex post-pass called between them from this small inlined wrapper: a call from inside either half costs the
   // half its registers (profiles/r2/convex_pairs.txt).
@@ -1878,7 +1625,6 @@ struct ArmEngine {
     r.sep = sep;
     return r;
   }
-#endif
   __device__ static __noinline__ void kinematics_only(WM* Wp, int lane) { kinematics(cmodel<real>(), *Wp, lane); }
   __device__ static __noinline__ bool dynamics_only(WM* Wp, int lane) { return dynamics(cmodel<real>(), *Wp, lane); }
   __device__ static __noinline__ void collide_only(WM* Wp, int lane) { SepAxis<real> sep = MJS_SEP_ZERO; bool cvx; collide(cmodel<real>(), *Wp, lane, sep, cvx); }
