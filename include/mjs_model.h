@@ -169,7 +169,7 @@ typedef struct MjsTask {
   int reward_type;
   int max_steps;           /* task-side step limit (RobotTask, base.py:47-51); 0 = none */
   int n_obj;
-  int action_dim;
+  int action_dim;              /* PointMass 2, Reach 3, Planar Push 2; Button Push 7 = ABS_JOINT_ACTION (servoJ) or 4 = ABS_EEF_ACTION (servoL), robot_push_button.py:143-157 */
   int obs_dim;
   int tcp_site;            /* flange site id (robot tasks) */
   int arm_qadr;            /* first arm qpos/dof/ctrl index */
